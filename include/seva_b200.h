@@ -1,0 +1,183 @@
+/*
+ * seva_b200 — C ABI of the B200 (sm_100a) kernels behind the Seva denoising step.
+ *
+ * Every entry point takes plain device pointers, sizes and a cudaStream_t (passed as void*), returns 0 on
+ * success and non-zero on error (message via seva_last_error()).  There is no CPU fallback: on a
+ * device that is not sm_100 every compute call fails with an error.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo root):
+ *   seva_gemm_bf16            nn.Linear / nn.Conv2d call sites: seva/modules/transformer.py:11,30,52-56,187,200;
+ *                             seva/modules/layers.py:40,54,101,104,107,113,118; seva/model.py:48-57,173
+ *   seva_attn_fwd             F.scaled_dot_product_attention, seva/modules/transformer.py:70-71 (spatial 2D/3D + cross)
+ *   seva_timemix_attn         same call site reached from TransformerBlockTimeMix.forward, transformer.py:145-155
+ *   seva_groupnorm_*          GroupNorm32 / nn.GroupNorm (+SiLU, +dense scale/shift): layers.py:61-63,99-100,110-111,
+ *                             124-131; transformer.py:186; model.py:170-172
+ *   seva_layernorm            nn.LayerNorm, transformer.py:102-104,124,141-143
+ *   seva_plucker              seva/geometry.py:119-165 get_plucker_coordinates
+ *   seva_resize_bilinear_ac   F.interpolate(..., mode="bilinear", align_corners=True), layers.py:126-128
+ *   seva_sigma_quantize       DiscreteDenoiser.sigma_to_idx/idx_to_sigma + EpsScaling: sampling.py:46-54,126-131
+ *   seva_denoise_prepare      DiscreteDenoiser.__call__ input side (replace-blend, c_in) + SGMWrapper concat:
+ *                             seva/sampling.py:146-150, seva/model.py:227; also VanillaCFG `cat([x]*2)`, :242
+ *   seva_denoise_finish       denoiser output side `net * c_out + input * c_skip`: sampling.py:150-152
+ *   seva_add_noise            sampler_step noise injection: sampling.py:361-362
+ *   seva_cfg_euler_step       guider combine + to_d + Euler update: sampling.py:24,213,252-265,366-368
+ *   seva_multiview_scale      MultiviewScaleRule + get_camera_dist: sampling.py:160-187, geometry.py:12-40
+ *   seva_pack_nchw/unpack     NCHW <-> channels-last boundary of Seva.forward (model.py:176-216)
+ *   seva_upsample2x_pad       F.interpolate(scale_factor=2, mode="nearest"), layers.py:44
+ *   seva_im2col3x3_s2         Downsample's stride-2 3x3 conv gather, layers.py:54-58
+ *   seva_timestep_embedding   seva/modules/layers.py:11-32
+ *   seva_gemv_rows            small-M Linear (time_embed, emb_layers, cross-attention with one context token)
+ */
+#ifndef SEVA_B200_H_
+#define SEVA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Last error message of the calling thread ("" when none). */
+const char* seva_last_error(void);
+/* 0 when the current CUDA device is sm_100 (B200); non-zero (and an error message) otherwise. */
+int seva_check_device(void);
+/* Library / kernel ABI version. */
+int seva_version(void);
+
+/* ---- tensor-core GEMM / implicit-GEMM convolution ------------------------------------------- */
+typedef struct SevaGemm {
+  const void* A;       /* bf16 [a_rows, >=Kc], row stride lda elements                                  */
+  int64_t lda;
+  int64_t a_rows;      /* rows addressable through A (rows outside [0,a_rows) read as zero)            */
+  const void* W;       /* bf16 [N, ntaps*Kc] row-major (K-major), row stride ldw elements              */
+  int64_t ldw;
+  int32_t M, N, Kc;    /* output rows, output columns (before GEGLU halving), reduction per tap        */
+  int32_t ntaps;       /* 1 = plain GEMM, 9 = 3x3 conv over a zero-bordered flat image                 */
+  int32_t tap_wp;      /* padded image width Wp: tap t reads row m + (t/3-1)*Wp + (t%3-1)              */
+  const float* bias;   /* fp32 [N] or NULL                                                              */
+  const float* rowbias;/* fp32 [ceil(M/rowbias_rpi), Nout] or NULL; added to every row of a row group   */
+  int32_t rowbias_rpi;
+  const void* residual;/* bf16, addressed like out (same row map), row stride ldr; or NULL             */
+  int64_t ldr;
+  void* out;           /* bf16 (or fp32 when out_fp32) row stride ldo                                   */
+  int64_t ldo;
+  int32_t out_fp32;
+  int32_t geglu;       /* 1: W rows are tile-interleaved [x | gate]; out[:, j] = x_j * gelu(gate_j)     */
+  int32_t out_map;     /* 0: row m -> m.  1: compact (n, y, x) of an HxW image -> zero-bordered flat    */
+  int32_t H, Wd;       /*    row n*(H+2)*(Wd+2) + (y+1)*(Wd+2) + x+1                                     */
+  int32_t mask_border; /* 1: rows are zero-bordered flat (Hp x Wp per image): border rows written as 0 */
+  int32_t Hp, Wp;
+  int32_t bn;          /* N tile (multiple of 32, <= 256; GEGLU: multiple of 64); 0 = choose            */
+} SevaGemm;
+int seva_gemm_bf16(const SevaGemm* g, void* stream);
+/* N tile seva_gemm_bf16 will use for (N, geglu) when g->bn == 0 (weights for geglu are packed against it). */
+int seva_gemm_pick_bn(int32_t N, int32_t geglu);
+
+/* ---- attention -------------------------------------------------------------------------------- */
+/* o[b, i, h*64:(h+1)*64] = softmax_j(q[b,i,h,:] . k[b,j,h,:] * scale) v[b,j,h,:]; head dim 64, bf16.
+ * q/k/v/o: element (b, l, h, d) at base + b*bs + l*ld + h*64 + d (strides in elements). */
+int seva_attn_fwd(const void* q, const void* k, const void* v, void* o, int32_t B, int32_t Hh,
+                  int32_t Lq, int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
+                  int64_t bsq, int64_t bsk, int64_t bsv, int64_t bso, float scale, void* stream);
+/* Attention over the frame axis: tokens are rows (b*T + t)*S + s of qkv [B*T*S, 3*C] (q | k | v, C = Hh*64);
+ * for every (b, s, h) softmax over t' of the T frames.  out [B*T*S, C] (row stride ldo). */
+int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t T, int32_t S, int32_t Hh,
+                      int64_t ldqkv, int64_t ldo, float scale, void* stream);
+
+/* ---- normalisation ---------------------------------------------------------------------------- */
+/* Per-(image, channel) sum and sum of squares over rpi rows: sums[n, c, 0:2] (fp32, zeroed inside). */
+int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
+                         float* sums, void* stream);
+typedef struct SevaGNApply {
+  const void* x; int64_t ldx;     /* bf16 input, zero-bordered flat (in_padded=1) or compact rows        */
+  void* y; int64_t ldy;           /* bf16 output                                                          */
+  const float* sums;              /* from seva_groupnorm_stats: [Nimg, C, 2]                              */
+  const float* gamma; const float* beta;  /* fp32 [C]                                                     */
+  int32_t Nimg, H, Wd, C, groups;
+  float eps;
+  int32_t in_padded, out_padded;  /* layout of x / y (padded output gets a zero border)                   */
+  int32_t silu;
+  const float* dense;             /* optional fp32 [Nimg, H*Wd, 6] resized Plucker map, or NULL           */
+  const float* dense_w;           /* fp32 [2C, 6] (scale rows first, then shift rows)                     */
+  const float* dense_b;           /* fp32 [2C]                                                            */
+} SevaGNApply;
+int seva_groupnorm_apply(const SevaGNApply* p, void* stream);
+/* y[m, :] = LayerNorm(x[m, :]) * gamma + beta, eps inside sqrt; bf16 in/out, fp32 statistics. */
+int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, const float* gamma,
+                   const float* beta, int32_t M, int32_t C, float eps, void* stream);
+
+/* ---- camera geometry --------------------------------------------------------------------------- */
+/* Plucker ray map.  w2c [T,4,4], w2c_src [4,4], Kpix [T,3,3] intrinsics already in latent-pixel units
+ * (the caller performs the reference's in-place `intrinsics[:, :2] *= (w, h)`, geometry.py:149-154).
+ * out [T, 6, h, w] fp32 (reference layout: ray direction, then centre x direction). */
+int seva_plucker(const float* w2c_src, const float* w2c, const float* Kpix, float* out, int32_t T,
+                 int32_t h, int32_t w, void* stream);
+/* Bilinear align_corners=True resize of src [N, C, hs, ws] fp32 to channels-last dst [N, hd*wd, C] fp32. */
+int seva_resize_bilinear_ac(const float* src, float* dst, int32_t N, int32_t C, int32_t hs,
+                            int32_t ws, int32_t hd, int32_t wd, void* stream);
+/* MultiviewScaleRule (sampling.py:160-187): scale_out[t] = min_scale when an input frame (input_mask[j] != 0)
+ * has rotation distance < 10 deg, translation distance < 1e-5 and identical K, else scale_in.
+ * c2w [T,4,4], K [T,3,3] fp32; scale_in scalar (scale_is_vector=0) or [T]; close_out optional [T] (0/1). */
+int seva_multiview_scale(const float* c2w, const float* K, const uint8_t* input_mask,
+                         const float* scale_in, int32_t scale_is_vector, float min_scale,
+                         float* scale_out, uint8_t* close_out, int32_t T, void* stream);
+
+/* ---- sampler-side fused elementwise ------------------------------------------------------------ */
+/* sigma -> index of the nearest table entry (first minimum, bit-exact with the reference argmin,
+ * sampling.py:126-128), quantised sigma and EpsScaling c_in = 1/sqrt(s^2+1), c_out = -s (sampling.py:46-54). */
+int seva_sigma_quantize(const float* sigma, const float* table, int32_t ntable, int64_t* idx_out,
+                        float* sigma_q, float* c_in, float* c_out, int32_t N, void* stream);
+/* out = x + eps * sqrt(sigma_hat^2 - sigma^2), per frame (sampling.py:361-362).  [T, per_frame] fp32. */
+int seva_add_noise(const float* x, const float* eps, const float* sigma, const float* sigma_hat,
+                   float* out, int32_t T, int64_t per_frame, void* stream);
+/* Network input assembly (DiscreteDenoiser.__call__ input side + SGMWrapper concat) for N images:
+ *   blended = x*(1-m) + r*m with (r, m) = replace[:, 0:4], replace[:, 4] (replace may be NULL: blended = x)
+ *   net_in (bf16, zero-bordered flat [N, (h+2)*(w+2), ldn], ldn >= 16): ch 0-3 = blended*c_in[n],
+ *   ch 4-10 = concat, remaining channels and the border zero;  blended_out fp32 [N,4,h,w].
+ * x [x_frames,4,h,w] (image n reads frame n % x_frames: pass x_frames = N/2 to fuse `cat([x]*2)`,
+ * sampling.py:242); replace [N,5,h,w]; concat [N,7,h,w]; c_in [N]; all fp32. */
+int seva_denoise_prepare(const float* x, const float* replace, const float* concat,
+                         const float* c_in, void* net_in, int64_t ldn, float* blended_out,
+                         int32_t N, int32_t x_frames, int32_t h, int32_t w, void* stream);
+/* Denoiser output side: out[n,c,y,x] = eps[n, (y+1)*(w+2)+x+1, c] * c_out[n] + blended[n,c,y,x].
+ * eps is the fp32 zero-bordered flat network output with row stride lde (>= 4). */
+int seva_denoise_finish(const float* eps, int64_t lde, const float* blended, const float* c_out,
+                        float* out, int32_t N, int32_t h, int32_t w, void* stream);
+/* Guidance combine + Euler update in one launch:
+ *   den = u + scale[t]*(c - u), (u, c) = denoised[0:T], denoised[T:2T];
+ *   x_next = x + (sigma_next[t] - sigma_hat[t]) * (x - den) / sigma_hat[t]
+ * x, x_next [T, per_frame] fp32 (may alias), per_frame % 4 == 0; denoised_out optional. */
+int seva_cfg_euler_step(const float* x, const float* denoised, const float* scale,
+                        const float* sigma_hat, const float* sigma_next, float* x_next,
+                        float* denoised_out, int32_t T, int64_t per_frame, void* stream);
+/* NCHW fp32 [N,C,h,w] -> bf16 zero-bordered flat [N,(h+2)(w+2),ld] (channels C..ld-1 zero), and back
+ * from an fp32 zero-bordered flat tensor (first C channels) to NCHW fp32. */
+int seva_pack_nchw(const float* src, void* dst, int64_t ld, int32_t N, int32_t C, int32_t h,
+                   int32_t w, void* stream);
+int seva_unpack_nchw(const float* src, int64_t ld, float* dst, int32_t N, int32_t C, int32_t h,
+                     int32_t w, void* stream);
+
+/* ---- data movement ----------------------------------------------------------------------------- */
+/* Nearest 2x upsample between zero-bordered flat images: src [N,(h+2)(w+2),lds] -> dst [N,(2h+2)(2w+2),ldd]. */
+int seva_upsample2x_pad(const void* src, int64_t lds, void* dst, int64_t ldd, int32_t N, int32_t h,
+                        int32_t w, int32_t C, void* stream);
+/* Gather for a 3x3 stride-2 pad-1 conv: src zero-bordered flat [N,(h+2)(w+2),lds] ->
+ * dst compact [N*(h/2)*(w/2), 9*C] with column tap*C + c. */
+int seva_im2col3x3_s2(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
+                      int32_t C, void* stream);
+/* fp32 rows -> bf16 rows (used for packing small inputs). */
+int seva_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* ---- small dense ops ---------------------------------------------------------------------------- */
+/* out[n, 0:dim] = [cos(t[n]*f_k) | sin(t[n]*f_k)], f_k = exp(-ln(max_period)*k/(dim/2)); t int64. */
+int seva_timestep_embedding(const int64_t* t, float* out, int32_t N, int32_t dim, float max_period,
+                            void* stream);
+/* out[m, n] = act_in(x[m, :]) . W[n, :] + bias[n]; x fp32 [M,K] (M small), W bf16 [N,K], out fp32.
+ * silu_in: apply SiLU to x first.  silu_out: apply SiLU to the result. */
+int seva_gemv_rows(const float* x, const void* W, const float* bias, float* out, int32_t M,
+                   int32_t N, int32_t K, int32_t silu_in, int32_t silu_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEVA_B200_H_ */

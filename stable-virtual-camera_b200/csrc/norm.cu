@@ -1,0 +1,368 @@
+// GroupNorm (statistics + fused apply/SiLU/Plucker modulation) and LayerNorm for channels-last bf16.
+// HBM-bound kernels: one read + one write of the activation, fp32 statistics.
+//
+// Reference: GroupNorm32 (seva/modules/layers.py:61-63) used at layers.py:99,110 and model.py:171,
+// nn.GroupNorm eps=1e-6 at transformer.py:186, the dense scale/shift of ResBlock.forward
+// (layers.py:124-131), nn.LayerNorm at transformer.py:102-104,124,141-143.
+#include "common.cuh"
+#include "../../include/seva_b200.h"
+
+namespace seva {
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// GroupNorm statistics: per (image, channel) sum / sum of squares, fp32, atomically merged.
+// Thread owns a fixed 8-channel vector and walks rows; zero border rows of padded images add 0.
+// ------------------------------------------------------------------------------------------------
+constexpr int kStatRowsPerBlock = 128;
+
+__global__ void __launch_bounds__(512)
+gn_stats_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rpi, int C, float* sums) {
+  extern __shared__ float red[];  // [blockDim.x][16]
+  const int CV = C >> 3;
+  const int cv = threadIdx.x % CV;
+  const int r0 = threadIdx.x / CV;
+  const int RPB = blockDim.x / CV;
+  const int n = blockIdx.y;
+  const int row_begin = blockIdx.x * kStatRowsPerBlock;
+  const int row_end = min(rpi, row_begin + kStatRowsPerBlock);
+  float s[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.0f;
+  const __nv_bfloat16* base = x + ((long long)n * rpi) * ldx + cv * 8;
+#pragma unroll 4
+  for (int r = row_begin + r0; r < row_end; r += RPB) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(base + (long long)r * ldx));
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float a = bf16_lo(w[i]), b = bf16_hi(w[i]);
+      s[2 * i] += a;
+      q[2 * i] = fmaf(a, a, q[2 * i]);
+      s[2 * i + 1] += b;
+      q[2 * i + 1] = fmaf(b, b, q[2 * i + 1]);
+    }
+  }
+  float* mine = red + threadIdx.x * 16;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    mine[2 * i] = s[i];
+    mine[2 * i + 1] = q[i];
+  }
+  __syncthreads();
+  // threads with r0 == 0 fold the RPB partials of their channel vector, then one atomic per value
+  if (r0 == 0) {
+    float acc[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = mine[i];
+    for (int k = 1; k < RPB; ++k) {
+      const float* o = red + (k * CV + cv) * 16;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) acc[i] += o[i];
+    }
+    float* dst = sums + ((long long)n * C + cv * 8) * 2;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) atomicAdd(dst + i, acc[i]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// GroupNorm apply (+SiLU, + h*(1+scale)+shift with scale/shift = W[2C,6] p + b recomputed per pixel)
+// Thread owns a fixed 4-channel group (8-byte accesses, 256 B per warp) and walks pixels, so the
+// per-channel affine and the 4x2x7 dense weights stay in registers.
+// ------------------------------------------------------------------------------------------------
+constexpr int kApplyPixPerBlock = 96;
+
+struct GNApplyArgs {
+  const __nv_bfloat16* x;
+  long long ldx;
+  __nv_bfloat16* y;
+  long long ldy;
+  const float* sums;
+  const float* gamma;
+  const float* beta;
+  int H, W, C, groups;
+  float eps;
+  int in_padded, out_padded, silu;
+  const float* dense;
+  const float* dense_w;
+  const float* dense_b;
+};
+
+template <bool kDense>
+__global__ void __launch_bounds__(640)
+gn_apply_kernel(const GNApplyArgs a) {
+  extern __shared__ float gstat[];  // [groups][2] mean, rstd
+  const int n = blockIdx.y;
+  const int cpg = a.C / a.groups;
+  const int HW = a.H * a.W;
+  const int Wp = a.W + 2;
+  const long long rpi_pad = (long long)(a.H + 2) * Wp;
+  for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
+    const float* sp = a.sums + ((long long)n * a.C + g * cpg) * 2;
+    float s = 0.f, q = 0.f;
+    for (int c = 0; c < cpg; ++c) {
+      s += sp[2 * c];
+      q += sp[2 * c + 1];
+    }
+    const float cnt = (float)cpg * (float)HW;
+    const float mean = s / cnt;
+    const float var = fmaxf(q / cnt - mean * mean, 0.0f);
+    gstat[2 * g] = mean;
+    gstat[2 * g + 1] = rsqrtf(var + a.eps);
+  }
+  __syncthreads();
+
+  const int CG = a.C >> 2;
+  const int cg = threadIdx.x % CG;
+  const int pl = threadIdx.x / CG;
+  const int PPB = blockDim.x / CG;
+  const int c0 = cg * 4;
+  float sa[4], sb[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + i;
+    const int g = c / cpg;
+    const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
+    const float ga = a.gamma[c], be = a.beta[c];
+    sa[i] = rstd * ga;
+    sb[i] = fmaf(-mean, rstd * ga, be);
+  }
+  float ws[4][6], wh[4][6], bs[4], bh[4];
+  if (kDense) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        ws[i][k] = a.dense_w[(long long)(c0 + i) * 6 + k];
+        wh[i][k] = a.dense_w[(long long)(a.C + c0 + i) * 6 + k];
+      }
+      bs[i] = 1.0f + a.dense_b[c0 + i];  // fold the "1 +" of h*(1+scale)
+      bh[i] = a.dense_b[a.C + c0 + i];
+    }
+  }
+
+  const int p_begin = blockIdx.x * kApplyPixPerBlock;
+  const int p_end = min(HW, p_begin + kApplyPixPerBlock);
+  const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
+  const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
+#pragma unroll 2
+  for (int p = p_begin + pl; p < p_end; p += PPB) {
+    const int yy = p / a.W;
+    const int xx = p - yy * a.W;
+    const long long prow = (long long)(yy + 1) * Wp + xx + 1;
+    const long long in_row = in_img + (a.in_padded ? prow : (long long)p);
+    const long long out_row = out_img + (a.out_padded ? prow : (long long)p);
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(a.x + in_row * a.ldx + c0));
+    float v[4] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y)};
+    float pk[6];
+    if (kDense) {
+      const float2* dp = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p) * 6);
+      const float2 d0 = __ldg(dp), d1 = __ldg(dp + 1), d2 = __ldg(dp + 2);
+      pk[0] = d0.x; pk[1] = d0.y; pk[2] = d1.x; pk[3] = d1.y; pk[4] = d2.x; pk[5] = d2.y;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float h = fmaf(v[i], sa[i], sb[i]);
+      if (a.silu) h = silu_f(h);
+      if (kDense) {
+        float sc = bs[i], sh = bh[i];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          sc = fmaf(ws[i][k], pk[k], sc);
+          sh = fmaf(wh[i][k], pk[k], sh);
+        }
+        h = fmaf(h, sc, sh);
+      }
+      v[i] = h;
+    }
+    uint2 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    *reinterpret_cast<uint2*>(a.y + out_row * a.ldy + c0) = o;
+  }
+
+  // zero border of a padded output image (first pixel-chunk block of each image)
+  if (a.out_padded && blockIdx.x == 0) {
+    const int Hp = a.H + 2;
+    const int nborder = 2 * Wp + 2 * a.H;
+    for (int i = pl; i < nborder; i += PPB) {
+      int yy, xx;
+      if (i < Wp) { yy = 0; xx = i; }
+      else if (i < 2 * Wp) { yy = Hp - 1; xx = i - Wp; }
+      else { const int k = i - 2 * Wp; yy = 1 + (k >> 1); xx = (k & 1) ? Wp - 1 : 0; }
+      const long long row = out_img + (long long)yy * Wp + xx;
+      *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm: one warp per row, row kept in registers (NP bf16 pairs per lane), two-pass variance.
+// ------------------------------------------------------------------------------------------------
+template <int NP>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y,
+                 long long ldy, const float* __restrict__ gamma, const float* __restrict__ beta, int M,
+                 int C, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + warp;
+  if (row >= M) return;
+  const uint32_t* xp = reinterpret_cast<const uint32_t*>(x + row * ldx);
+  float v[2 * NP];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const uint32_t u = __ldg(xp + k * 32 + lane);
+    v[2 * k] = bf16_lo(u);
+    v[2 * k + 1] = bf16_hi(u);
+    s += v[2 * k] + v[2 * k + 1];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < 2 * NP; ++k) {
+    const float d = v[k] - mean;
+    q = fmaf(d, d, q);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q / (float)C + eps);
+  uint32_t* yp = reinterpret_cast<uint32_t*>(y + row * ldy);
+  const float2* g2 = reinterpret_cast<const float2*>(gamma);
+  const float2* b2 = reinterpret_cast<const float2*>(beta);
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const float2 g = __ldg(g2 + k * 32 + lane), b = __ldg(b2 + k * 32 + lane);
+    const float o0 = fmaf((v[2 * k] - mean) * rstd, g.x, b.x);
+    const float o1 = fmaf((v[2 * k + 1] - mean) * rstd, g.y, b.y);
+    yp[k * 32 + lane] = pack_bf16x2(o0, o1);
+  }
+}
+
+// generic fallback (any even C): three passes over the row through L1/L2
+__global__ void __launch_bounds__(256)
+layernorm_generic_kernel(const __nv_bfloat16* __restrict__ x, long long ldx,
+                         __nv_bfloat16* __restrict__ y, long long ldy,
+                         const float* __restrict__ gamma, const float* __restrict__ beta, int M, int C,
+                         float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + warp;
+  if (row >= M) return;
+  const __nv_bfloat16* xp = x + row * ldx;
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) s += __bfloat162float(xp[c]);
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / (float)C;
+  float q = 0.f;
+  for (int c = lane; c < C; c += 32) {
+    const float d = __bfloat162float(xp[c]) - mean;
+    q = fmaf(d, d, q);
+  }
+  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q / (float)C + eps);
+  __nv_bfloat16* yp = y + row * ldy;
+  for (int c = lane; c < C; c += 32)
+    yp[c] = __float2bfloat16(fmaf((__bfloat162float(xp[c]) - mean) * rstd, gamma[c], beta[c]));
+}
+
+}  // namespace
+}  // namespace seva
+
+extern "C" int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
+                                    float* sums, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(x && sums, "seva_groupnorm_stats: null pointer");
+  SEVA_CHECK(Nimg > 0 && rpi > 0 && C > 0 && (C % 8) == 0 && (ldx % 8) == 0,
+             "seva_groupnorm_stats: need C %% 8 == 0 and ldx %% 8 == 0 (C=%d ldx=%lld)", C,
+             (long long)ldx);
+  SEVA_CHECK(C / 8 <= 512, "seva_groupnorm_stats: C too large (%d)", C);
+  SEVA_CHECK(((uintptr_t)x & 15) == 0, "seva_groupnorm_stats: x must be 16-byte aligned");
+  SEVA_CUDA(cudaMemsetAsync(sums, 0, sizeof(float) * 2 * (size_t)Nimg * C, stream));
+  const int CV = C / 8;
+  int rpb = 512 / CV;
+  if (rpb < 1) rpb = 1;
+  const int threads = CV * rpb;
+  dim3 grid((rpi + kStatRowsPerBlock - 1) / kStatRowsPerBlock, Nimg);
+  gn_stats_kernel<<<grid, threads, threads * 16 * sizeof(float), stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rpi, C, sums);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(p && p->x && p->y && p->sums && p->gamma && p->beta, "seva_groupnorm_apply: null pointer");
+  SEVA_CHECK(p->C > 0 && p->groups > 0 && (p->C % p->groups) == 0 && (p->C % 4) == 0,
+             "seva_groupnorm_apply: bad C=%d groups=%d", p->C, p->groups);
+  SEVA_CHECK((p->ldx % 4) == 0 && (p->ldy % 4) == 0, "seva_groupnorm_apply: ldx/ldy must be multiples of 4");
+  SEVA_CHECK(p->C / 4 <= 640, "seva_groupnorm_apply: C too large (%d)", p->C);
+  SEVA_CHECK(!p->dense || (p->dense_w && p->dense_b), "seva_groupnorm_apply: dense needs dense_w/dense_b");
+  GNApplyArgs a;
+  a.x = reinterpret_cast<const __nv_bfloat16*>(p->x);
+  a.ldx = p->ldx;
+  a.y = reinterpret_cast<__nv_bfloat16*>(p->y);
+  a.ldy = p->ldy;
+  a.sums = p->sums;
+  a.gamma = p->gamma;
+  a.beta = p->beta;
+  a.H = p->H;
+  a.W = p->Wd;
+  a.C = p->C;
+  a.groups = p->groups;
+  a.eps = p->eps;
+  a.in_padded = p->in_padded;
+  a.out_padded = p->out_padded;
+  a.silu = p->silu;
+  a.dense = p->dense;
+  a.dense_w = p->dense_w;
+  a.dense_b = p->dense_b;
+  const int CG = p->C / 4;
+  int ppb = 512 / CG;
+  if (ppb < 1) ppb = 1;
+  const int threads = CG * ppb;
+  const int HW = p->H * p->Wd;
+  dim3 grid((HW + kApplyPixPerBlock - 1) / kApplyPixPerBlock, p->Nimg);
+  const size_t smem = sizeof(float) * 2 * p->groups;
+  if (p->dense)
+    gn_apply_kernel<true><<<grid, threads, smem, stream>>>(a);
+  else
+    gn_apply_kernel<false><<<grid, threads, smem, stream>>>(a);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, const float* gamma,
+                              const float* beta, int32_t M, int32_t C, float eps, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(x && y && gamma && beta, "seva_layernorm: null pointer");
+  SEVA_CHECK(M > 0 && C > 0 && (C % 2) == 0 && (ldx % 2) == 0 && (ldy % 2) == 0,
+             "seva_layernorm: need even C/ldx/ldy");
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
+  const int grid = (M + 7) / 8;
+  if (C == 320)
+    layernorm_kernel<5><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else if (C == 640)
+    layernorm_kernel<10><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else if (C == 1280)
+    layernorm_kernel<20><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else if (C == 64)
+    layernorm_kernel<1><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else if (C == 128)
+    layernorm_kernel<2><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else if (C == 256)
+    layernorm_kernel<4><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  else
+    layernorm_generic_kernel<<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
