@@ -1,0 +1,476 @@
+"""Execution plan for one ``Seva.forward`` shape: packed weights, static workspaces, and a flat list of C-ABI
+kernel launches (see DESIGN.md "Data layout in HBM").
+
+Layouts
+  * "padded": bf16 [N*(H+2)*(W+2), C] channels-last flat image with a zero border (ResBlock / conv land); a 3x3
+    conv is nine row-shifted GEMM taps over it.
+  * "tokens": bf16 [N*H*W, C] (transformer land); "(b t)(h w) c -> b (t h w) c" (transformer.py:237) is a view.
+  * skip concats ``torch.cat([h, hs.pop()], 1)`` (model.py:207) are never materialised: both producers write
+    column slices of one buffer (row stride = C_h + C_skip).
+All buffers are allocated once per (N, T, h, w) and all launch descriptors are built once, so ``run()`` is a
+loop of foreign calls with constant arguments (and is CUDA-graph capturable).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib, ops, pack
+from ._lib import SevaB200Error
+from .model import (Downsample, MultiviewTransformer, ResBlock, Seva, Upsample)
+
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+# ----------------------------------------------------------------------------------------------------
+# weight packing
+# ----------------------------------------------------------------------------------------------------
+def _f32(p):
+    return p.detach().float().contiguous()
+
+
+def _pack_ff(ff, dev):
+    w, b = ff.net[0].proj.weight, ff.net[0].proj.bias
+    bn = ops.pick_bn(w.shape[0], True)
+    wp, bp = pack.pack_geglu(w, b, bn)
+    return dict(w1=wp, b1=bp, bn1=bn, w2=pack.pack_linear(ff.net[2].weight), b2=_f32(ff.net[2].bias))
+
+
+def _pack_attn_self(at):
+    return dict(wqkv=pack.pack_linear(torch.cat([at.to_q.weight, at.to_k.weight, at.to_v.weight], 0)),
+                wo=pack.pack_linear(at.to_out[0].weight), bo=_f32(at.to_out[0].bias))
+
+
+def _pack_attn_cross(at):
+    return dict(wq=pack.pack_linear(at.to_q.weight), wk=pack.pack_linear(at.to_k.weight),
+                wv=pack.pack_linear(at.to_v.weight), wo=pack.pack_linear(at.to_out[0].weight),
+                bo=_f32(at.to_out[0].bias))
+
+
+def _pack_ln(ln):
+    return dict(g=_f32(ln.weight), b=_f32(ln.bias), eps=float(ln.eps))
+
+
+def pack_weights(model: Seva) -> dict:
+    """id(module) -> dict of kernel-layout tensors (bf16 K-major matrices, fp32 vectors)."""
+    dev = next(model.parameters()).device
+    P: dict = {}
+    with torch.no_grad():
+        te = model.time_embed
+        P["time_embed"] = dict(w0=pack.pack_linear(te[0].weight), b0=_f32(te[0].bias),
+                               w2=pack.pack_linear(te[2].weight), b2=_f32(te[2].bias))
+        conv_in = model.input_blocks[0][0]
+        P["conv_in"] = dict(w=pack.pack_conv3x3(conv_in.weight, cin_pad=64), b=_f32(conv_in.bias))
+        P["out"] = dict(g=_f32(model.out[0].weight), b=_f32(model.out[0].bias), eps=float(model.out[0].eps),
+                        w=pack.pack_conv3x3(model.out[2].weight), cb=_f32(model.out[2].bias))
+        for m in model.modules():
+            if isinstance(m, ResBlock):
+                d = dict(
+                    g1=_f32(m.in_layers[0].weight), b1=_f32(m.in_layers[0].bias), eps1=float(m.in_layers[0].eps),
+                    w1=pack.pack_conv3x3(m.in_layers[2].weight), cb1=_f32(m.in_layers[2].bias),
+                    we=pack.pack_linear(m.emb_layers[1].weight), be=_f32(m.emb_layers[1].bias),
+                    wd=_f32(m.dense_emb_layers[0].weight.reshape(2 * m.channels, -1)),
+                    bd=_f32(m.dense_emb_layers[0].bias),
+                    g2=_f32(m.out_layers[0].weight), b2=_f32(m.out_layers[0].bias), eps2=float(m.out_layers[0].eps),
+                    w2=pack.pack_conv3x3(m.out_layers[3].weight), cb2=_f32(m.out_layers[3].bias))
+                if not isinstance(m.skip_connection, torch.nn.Identity):
+                    d["ws"] = pack.pack_conv1x1(m.skip_connection.weight)
+                    d["bs"] = _f32(m.skip_connection.bias)
+                P[id(m)] = d
+            elif isinstance(m, MultiviewTransformer):
+                assert len(m.transformer_blocks) == 1, "transformer depth > 1 is not wired into the plan yet"
+                tb, tm = m.transformer_blocks[0], m.time_mix_blocks[0]
+                P[id(m)] = dict(
+                    gn=dict(g=_f32(m.norm.weight), b=_f32(m.norm.bias), eps=float(m.norm.eps)),
+                    win=pack.pack_linear(m.proj_in.weight), bin=_f32(m.proj_in.bias),
+                    wout=pack.pack_linear(m.proj_out.weight), bout=_f32(m.proj_out.bias),
+                    s_attn1=_pack_attn_self(tb.attn1), s_attn2=_pack_attn_cross(tb.attn2), s_ff=_pack_ff(tb.ff, dev),
+                    s_n1=_pack_ln(tb.norm1), s_n2=_pack_ln(tb.norm2), s_n3=_pack_ln(tb.norm3),
+                    t_nin=_pack_ln(tm.norm_in), t_ffin=_pack_ff(tm.ff_in, dev), t_attn1=_pack_attn_self(tm.attn1),
+                    t_attn2=_pack_attn_cross(tm.attn2), t_ff=_pack_ff(tm.ff, dev),
+                    t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3))
+            elif isinstance(m, Downsample):
+                P[id(m)] = dict(w=pack.pack_conv3x3(m.op.weight), b=_f32(m.op.bias))
+            elif isinstance(m, Upsample):
+                P[id(m)] = dict(w=pack.pack_conv3x3(m.conv.weight), b=_f32(m.conv.bias))
+    return P
+
+
+# ----------------------------------------------------------------------------------------------------
+# plan
+# ----------------------------------------------------------------------------------------------------
+class Engine:
+    def __init__(self, model: Seva, packed: dict, n: int, num_frames: int, h: int, w: int, ctx_len: int):
+        p = model.params
+        nlev = len(p.channel_mult)
+        if h % (1 << (nlev - 1)) or w % (1 << (nlev - 1)):
+            raise SevaB200Error(f"latent size {h}x{w} must be divisible by {1 << (nlev - 1)}")
+        self.lib = _lib.load()
+        self.dev = next(model.parameters()).device
+        self.P = packed
+        self.N, self.T, self.B = n, num_frames, n // num_frames
+        self.h, self.w, self.L = h, w, ctx_len
+        self.ctx_dim = p.context_dim
+        self.unflatten = set(p.unflatten_names)
+        self.HW = [(h >> l, w >> l) for l in range(nlev)]
+        self.calls: list = []
+        self.meta: list = []
+        self.keep: list = []   # ctypes structs / tensors referenced by raw pointer
+        self.bufs: dict = {}
+        self.n_launch = 0
+        self.timing_sink: list | None = None  # set by bench.py to collect per-launch CUDA events
+
+        # static inputs
+        self.net_in = self.buf("net_in", self.rows_p(0), 64)
+        self.t_in = torch.zeros(n, device=self.dev, dtype=torch.int64)
+        self.ctx_in = torch.zeros(n, ctx_len, p.context_dim, device=self.dev, dtype=F32)
+        self.ctx0_in = torch.zeros(self.B, ctx_len, p.context_dim, device=self.dev, dtype=F32)
+        self.dense_in = torch.zeros(n, p.dense_in_channels, h, w, device=self.dev, dtype=F32)
+        self.eps = torch.zeros(self.rows_p(0), p.out_channels, device=self.dev, dtype=F32)
+        self._build(model)
+
+    # ---- helpers -------------------------------------------------------------------------------
+    def rows_p(self, l):
+        H, W = self.HW[l]
+        return self.N * (H + 2) * (W + 2)
+
+    def rows_c(self, l):
+        H, W = self.HW[l]
+        return self.N * H * W
+
+    def buf(self, name, rows, cols, dtype=BF16):
+        key = (name, rows, cols, dtype)
+        t = self.bufs.get(key)
+        if t is None:
+            t = torch.zeros(rows, cols, device=self.dev, dtype=dtype)
+            self.bufs[key] = t
+        return t
+
+    def add(self, fn, *args, flops: float = 0.0, nbytes: float = 0.0, tag: str = ""):
+        """Append one kernel launch; flops / nbytes are the ALGORITHMIC work of the reference op it replaces
+        (2*MAC for Linear/conv on unpadded pixels, 4*B*H*Lq*Lk*D for attention, activation bytes for norms)."""
+        self.calls.append((fn, args))
+        self.meta.append((fn.__name__, tag, float(flops), float(nbytes)))
+        self.n_launch += 1
+
+    # ---- op emitters (each appends exactly one kernel launch unless noted) ---------------------
+    def gemm(self, A, W, out, *, bias=None, M=None, ntaps=1, tap_wp=0, rowbias=None, rowbias_rpi=0, residual=None,
+             out_fp32=False, geglu=False, out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, Kc=None,
+             alg_rows=None, alg_k=None):
+        M = A.shape[0] if M is None else M
+        g = ops.make_gemm(A_ptr=A.data_ptr(), lda=A.stride(0), a_rows=A.shape[0], W_ptr=W.data_ptr(),
+                          ldw=W.stride(0), M=M, N=W.shape[0], Kc=A.shape[1] if Kc is None else Kc,
+                          out_ptr=out.data_ptr(), ldo=out.stride(0), ntaps=ntaps, tap_wp=tap_wp,
+                          bias_ptr=None if bias is None else bias.data_ptr(),
+                          rowbias_ptr=None if rowbias is None else rowbias.data_ptr(), rowbias_rpi=rowbias_rpi,
+                          residual_ptr=None if residual is None else residual.data_ptr(),
+                          ldr=0 if residual is None else residual.stride(0), out_fp32=out_fp32, geglu=geglu,
+                          out_map=out_map, H=H, Wd=Wd, mask_border=mask_border, Hp=Hp, Wp=Wp, bn=bn)
+        self.keep += [g, A, W, out, bias, rowbias, residual]
+        m_alg = M if alg_rows is None else alg_rows
+        kk = (A.shape[1] if Kc is None else Kc) if alg_k is None else alg_k
+        self.add(self.lib.seva_gemm_bf16, C.byref(g), flops=2.0 * m_alg * W.shape[0] * kk * ntaps,
+                 tag="conv3x3" if ntaps == 9 else ("geglu" if geglu else "linear"))
+
+    def conv3x3(self, x, l, W9, bias, out, *, rowbias=None, residual=None, out_fp32=False, alg_k=None):
+        H, Wd = self.HW[l]
+        self.gemm(x, W9, out, bias=bias, ntaps=9, tap_wp=Wd + 2, rowbias=rowbias, rowbias_rpi=(H + 2) * (Wd + 2),
+                  residual=residual, out_fp32=out_fp32, mask_border=True, Hp=H + 2, Wp=Wd + 2,
+                  alg_rows=self.rows_c(l), alg_k=alg_k)
+
+    def gn(self, x, l, C_, gamma, beta, eps, out, *, in_padded=True, out_padded=True, silu=False, dense=None,
+           dense_w=None, dense_b=None):
+        """GroupNorm: stats launch (+ memset inside) and apply launch."""
+        H, Wd = self.HW[l]
+        rpi = (H + 2) * (Wd + 2) if in_padded else H * Wd
+        sums = self.buf("gn_sums", self.N, 2 * C_, F32)
+        act = 2.0 * self.N * H * Wd * C_
+        self.add(self.lib.seva_groupnorm_stats, x.data_ptr(), x.stride(0), self.N, rpi, C_, sums.data_ptr(),
+                 nbytes=act, tag="gn_stats")
+        pa = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
+                               sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(),
+                               n_img=self.N, H=H, Wd=Wd, Cc=C_, groups=32, eps=eps, in_padded=in_padded,
+                               out_padded=out_padded, silu=silu,
+                               dense_ptr=None if dense is None else dense.data_ptr(),
+                               dense_w_ptr=None if dense_w is None else dense_w.data_ptr(),
+                               dense_b_ptr=None if dense_b is None else dense_b.data_ptr())
+        self.keep += [pa, x, out, gamma, beta, dense, dense_w, dense_b]
+        self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act, tag="gn_apply")
+
+    def ln(self, x, nrm, out):
+        self.add(self.lib.seva_layernorm, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0),
+                 nrm["g"].data_ptr(), nrm["b"].data_ptr(), x.shape[0], x.shape[1], nrm["eps"],
+                 nbytes=4.0 * x.shape[0] * x.shape[1], tag="layernorm")
+        self.keep += [x, out]
+
+    def gemv(self, x, W, bias, out, *, silu_in=False, silu_out=False):
+        M, K = x.shape
+        self.add(self.lib.seva_gemv_rows, x.data_ptr(), W.data_ptr(), None if bias is None else bias.data_ptr(),
+                 out.data_ptr(), M, W.shape[0], K, int(silu_in), int(silu_out))
+        self.keep += [x, W, bias, out]
+
+    # ---- network -------------------------------------------------------------------------------
+    def _build(self, model: Seva):
+        p = model.params
+        N, lib = self.N, self.lib
+        mc, ted = p.model_channels, p.model_channels * 4
+        # time embedding (layers.py:11-32, model.py:47-52,185-186)
+        temb = self.buf("temb", N, mc, F32)
+        e1 = self.buf("temb1", N, ted, F32)
+        self.emb = self.buf("emb", N, ted, F32)
+        te = self.P["time_embed"]
+        self.add(lib.seva_timestep_embedding, self.t_in.data_ptr(), temb.data_ptr(), N, mc, 10000.0)
+        self.gemv(temb, te["w0"], te["b0"], e1, silu_out=True)
+        self.gemv(e1, te["w2"], te["b2"], self.emb)
+        # Plucker map resized once per level (layers.py:126-128), channels-last fp32
+        self.dense = []
+        for l, (H, Wd) in enumerate(self.HW):
+            d = self.buf(f"dense{l}", N, H * Wd * p.dense_in_channels, F32)
+            self.add(lib.seva_resize_bilinear_ac, self.dense_in.data_ptr(), d.data_ptr(), N, p.dense_in_channels,
+                     self.h, self.w, H, Wd)
+            self.dense.append(d)
+
+        # ---- static schedule of where every block output lives (virtual skip concat) -----------
+        in_blocks = list(model.input_blocks)
+        out_blocks = list(model.output_blocks)
+        in_level, in_ch = [], []
+        lvl, ch = 0, mc
+        for i, blk in enumerate(in_blocks):
+            for layer in blk:
+                if isinstance(layer, ResBlock):
+                    ch = layer.out_channels
+                elif isinstance(layer, Downsample):
+                    lvl += 1
+                    ch = layer.out_channels
+            in_level.append(lvl)
+            in_ch.append(ch)
+        h_dest, skip_dest, cats = [], [None] * len(in_blocks), []
+        ch_h, lvl_o = ch, lvl
+        for k, blk in enumerate(out_blocks):
+            i = len(in_blocks) - 1 - k
+            assert in_level[i] == lvl_o, "skip / decoder resolution mismatch"
+            cat = self.buf(f"cat{k}", self.rows_p(lvl_o), ch_h + in_ch[i])
+            cats.append(cat)
+            h_dest.append(cat[:, :ch_h])
+            skip_dest[i] = cat[:, ch_h:]
+            for layer in blk:
+                if isinstance(layer, ResBlock):
+                    ch_h = layer.out_channels
+                elif isinstance(layer, Upsample):
+                    lvl_o -= 1
+        final_h = self.buf("final_h", self.rows_p(0), ch_h)
+
+        # ---- encoder ----------------------------------------------------------------------------
+        ci = self.P["conv_in"]
+        self.conv3x3(self.net_in, 0, ci["w"], ci["b"], skip_dest[0], alg_k=p.in_channels)
+        x, lvl = skip_dest[0], 0
+        for i in range(1, len(in_blocks)):
+            x, lvl = self._block(in_blocks[i], x, lvl, skip_dest[i], f"in{i}")
+        # ---- middle -----------------------------------------------------------------------------
+        x, lvl = self._block(model.middle_block, x, lvl, h_dest[0], "mid")
+        # ---- decoder ----------------------------------------------------------------------------
+        for k, blk in enumerate(out_blocks):
+            dest = h_dest[k + 1] if k + 1 < len(out_blocks) else final_h
+            x, lvl = self._block(blk, cats[k], lvl, dest, f"out{k}")
+        # ---- head (model.py:170-174) ------------------------------------------------------------
+        po = self.P["out"]
+        hn = self.buf("final_n", self.rows_p(0), ch_h)
+        self.gn(final_h, 0, ch_h, po["g"], po["b"], po["eps"], hn, silu=True)
+        self.conv3x3(hn, 0, po["w"], po["cb"], self.eps, out_fp32=True)
+
+    def _block(self, blk, x, lvl, dest, tag):
+        layers = list(blk)
+        for j, layer in enumerate(layers):
+            last = j == len(layers) - 1
+            if isinstance(layer, ResBlock):
+                out = dest if last else self.buf(f"res_out_{lvl}", self.rows_p(lvl), layer.out_channels)
+                self._resblock(layer, x, lvl, out)
+            elif isinstance(layer, MultiviewTransformer):
+                out = dest if last else self.buf(f"mvt_out_{lvl}", self.rows_p(lvl), layer.in_channels)
+                self._mvt(layer, x, lvl, out)
+            elif isinstance(layer, Downsample):
+                out = dest
+                self._down(layer, x, lvl, out)
+                lvl += 1
+            elif isinstance(layer, Upsample):
+                out = dest
+                self._up(layer, x, lvl, out)
+                lvl -= 1
+            else:
+                raise SevaB200Error(f"unexpected layer {type(layer).__name__} in {tag}")
+            x = out
+        return x, lvl
+
+    # ResBlock.forward, layers.py:120-139
+    def _resblock(self, m: ResBlock, x, l, out):
+        w = self.P[id(m)]
+        cin, cout = m.channels, m.out_channels
+        rp = self.rows_p(l)
+        h1 = self.buf(f"rb_h1_{l}", rp, cin)
+        self.gn(x, l, cin, w["g1"], w["b1"], w["eps1"], h1, silu=True, dense=self.dense[l], dense_w=w["wd"],
+                dense_b=w["bd"])
+        emb_out = self.buf(f"rb_emb_{cout}", self.N, cout, F32)
+        self.gemv(self.emb, w["we"], w["be"], emb_out, silu_in=True)
+        h2 = self.buf(f"rb_h2_{l}", rp, cout)
+        self.conv3x3(h1, l, w["w1"], w["cb1"], h2, rowbias=emb_out)
+        h3 = self.buf(f"rb_h3_{l}", rp, cout)
+        self.gn(h2, l, cout, w["g2"], w["b2"], w["eps2"], h3, silu=True)
+        if "ws" in w:
+            H, Wd = self.HW[l]
+            skip = self.buf(f"rb_skip_{l}", rp, cout)
+            self.gemm(x, w["ws"], skip, bias=w["bs"], mask_border=True, Hp=H + 2, Wp=Wd + 2,
+                      alg_rows=self.rows_c(l))
+        else:
+            skip = x
+        self.conv3x3(h3, l, w["w2"], w["cb2"], out, residual=skip)
+
+    # Downsample.forward, layers.py:56-58: stride-2 conv = gather + GEMM, written into the next level's border image
+    def _down(self, m: Downsample, x, l, out):
+        w = self.P[id(m)]
+        H, Wd = self.HW[l]
+        Ho, Wo = self.HW[l + 1]
+        col = self.buf(f"im2col_{l}", self.N * Ho * Wo, 9 * m.channels)
+        self.add(self.lib.seva_im2col3x3_s2, x.data_ptr(), x.stride(0), col.data_ptr(), self.N, H, Wd, m.channels)
+        self.keep += [x]
+        self.gemm(col, w["w"], out, bias=w["b"], out_map=1, H=Ho, Wd=Wo)
+
+    # Upsample.forward, layers.py:42-46
+    def _up(self, m: Upsample, x, l, out):
+        w = self.P[id(m)]
+        H, Wd = self.HW[l]
+        up = self.buf(f"up_{l - 1}", self.rows_p(l - 1), m.channels)
+        self.add(self.lib.seva_upsample2x_pad, x.data_ptr(), x.stride(0), up.data_ptr(), up.stride(0), self.N, H,
+                 Wd, m.channels)
+        self.keep += [x]
+        self.conv3x3(up, l - 1, w["w"], w["b"], out)
+
+    # cross-attention with a single context token is a per-image vector: softmax over one key is 1, so
+    # attn2(x, ctx) = to_out(to_v(ctx)) for every query (transformer.py:59-74 with Lk = 1).
+    def _cross_vec(self, wa, ctx_rows, C_, tag):
+        R = ctx_rows.shape[0]
+        v = self.buf(f"xv_{tag}_{C_}", R, C_, F32)
+        o = self.buf(f"xo_{tag}_{C_}", R, C_, F32)
+        self.gemv(ctx_rows, wa["wv"], None, v)
+        self.gemv(v, wa["wo"], wa["bo"], o)
+        return o
+
+    def _ff(self, x, nrm, ff, residual, out, l, C_in, tag):
+        rc = x.shape[0]
+        a = self.buf(f"tk_ln_{l}", rc, C_in)
+        self.ln(x, nrm, a)
+        inner = ff["w1"].shape[0] // 2
+        g = self.buf(f"tk_g_{l}", rc, inner)
+        self.gemm(a, ff["w1"], g, bias=ff["b1"], geglu=True, bn=ff["bn1"])
+        self.gemm(g, ff["w2"], out, bias=ff["b2"], residual=residual)
+
+    # MultiviewTransformer.forward, transformer.py:215-247
+    def _mvt(self, m: MultiviewTransformer, x, l, out):
+        w = self.P[id(m)]
+        C_, heads = m.in_channels, m.n_heads
+        H, Wd = self.HW[l]
+        S = H * Wd
+        rc = self.rows_c(l)
+        is3d = m.name in self.unflatten
+        T, B = self.T, self.B
+        ctx2 = self.ctx_in.reshape(self.N, self.L * self.ctx_dim)
+        ctx0 = self.ctx0_in.reshape(B, self.L * self.ctx_dim)
+
+        xn = self.buf(f"tk_xn_{l}", rc, C_)
+        self.gn(x, l, C_, w["gn"]["g"], w["gn"]["b"], w["gn"]["eps"], xn, out_padded=False)
+        x0 = self.buf(f"tk_x0_{l}", rc, C_)
+        self.gemm(xn, w["win"], x0, bias=w["bin"])
+
+        # ---- spatial block (TransformerBlock.forward, transformer.py:106-110)
+        a = self.buf(f"tk_ln_{l}", rc, C_)
+        self.ln(x0, w["s_n1"], a)
+        qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
+        self.gemm(a, w["s_attn1"]["wqkv"], qkv)
+        o = self.buf(f"tk_o_{l}", rc, C_)
+        bat, Lseq = (B, T * S) if is3d else (self.N, S)
+        ld = qkv.stride(0)
+        base = qkv.data_ptr()
+        self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
+                 ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
+                 flops=4.0 * bat * heads * Lseq * Lseq * 64, tag="attn3d" if is3d else "attn2d")
+        x1 = self.buf(f"tk_x1_{l}", rc, C_)
+        if self.L == 1:
+            xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, "s3" if is3d else "s2")
+            self.gemm(o, w["s_attn1"]["wo"], x1, bias=w["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq)
+        else:
+            x1a = self.buf(f"tk_x1a_{l}", rc, C_)
+            self.gemm(o, w["s_attn1"]["wo"], x1a, bias=w["s_attn1"]["bo"], residual=x0)
+            self._cross_general(w["s_attn2"], w["s_n2"], x1a, x1, l, C_, heads, bat, Lseq,
+                                self.ctx0_in if is3d else self.ctx_in)
+        x2 = self.buf(f"tk_x2_{l}", rc, C_)
+        self._ff(x1, w["s_n3"], w["s_ff"], x1, x2, l, C_, "s")
+
+        # ---- time-mix block (TransformerBlockTimeMix.forward, transformer.py:145-155), tokens stay (b t) s
+        y1 = self.buf(f"tk_y1_{l}", rc, C_)
+        self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin")
+        self.ln(y1, w["t_n1"], a)
+        self.gemm(a, w["t_attn1"]["wqkv"], qkv)
+        self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
+                 o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
+                 tag="timemix")
+        y2 = self.buf(f"tk_y2_{l}", rc, C_)
+        if self.L == 1:
+            xr = self._cross_vec(w["t_attn2"], ctx0, C_, "t")
+            self.gemm(o, w["t_attn1"]["wo"], y2, bias=w["t_attn1"]["bo"], residual=y1, rowbias=xr,
+                      rowbias_rpi=T * S)
+        else:
+            raise SevaB200Error("time-mix cross-attention with more than one context token is not implemented")
+        x3 = self.buf(f"tk_x3_{l}", rc, C_)
+        # x = x_spatial + ff(norm3(y2)): SkipConnect (transformer.py:158-165) folded into the residual
+        self._ff(y2, w["t_n3"], w["t_ff"], x2, x3, l, C_, "t")
+        # proj_out + input residual, written back to the zero-bordered layout (transformer.py:244-247)
+        self.gemm(x3, w["wout"], out, bias=w["bout"], residual=x, out_map=1, H=H, Wd=Wd)
+
+    def _cross_general(self, wa, nrm, xin, xout, l, C_, heads, bat, Lseq, ctx):
+        """attn2 with Lk > 1 context tokens: LN -> q, k/v from context -> flash attention -> to_out + residual."""
+        rc = xin.shape[0]
+        a = self.buf(f"tk_ln_{l}", rc, C_)
+        self.ln(xin, nrm, a)
+        q = self.buf(f"tk_q_{l}", rc, C_)
+        self.gemm(a, wa["wq"], q)
+        R = ctx.shape[0]
+        cb = self.buf(f"ctx_bf16_{R}", R * self.L, self.ctx_dim)
+        self.add(self.lib.seva_cast_f32_bf16, ctx.data_ptr(), cb.data_ptr(), ctx.numel())
+        k = self.buf(f"ctx_k_{R}_{C_}", R * self.L, C_)
+        v = self.buf(f"ctx_v_{R}_{C_}", R * self.L, C_)
+        self.gemm(cb, wa["wk"], k)
+        self.gemm(cb, wa["wv"], v)
+        o = self.buf(f"tk_o2_{l}", rc, C_)
+        assert R == bat
+        self.add(self.lib.seva_attn_fwd, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), bat, heads, Lseq,
+                 self.L, C_, C_, C_, C_, Lseq * C_, self.L * C_, self.L * C_, Lseq * C_, 0.125,
+                 flops=4.0 * bat * heads * Lseq * self.L * 64, tag="attn_cross")
+        self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin)
+
+    # ---- execution ------------------------------------------------------------------------------
+    def bind(self, t: torch.Tensor, ctx: torch.Tensor, dense: torch.Tensor) -> None:
+        """Copy the per-call conditioning into the plan's static input buffers (device-to-device)."""
+        self.t_in.copy_(t.reshape(-1))
+        self.ctx_in.copy_(ctx)
+        self.ctx0_in.copy_(ctx[:: self.T])
+        self.dense_in.copy_(dense)
+
+    def run(self, timing: list | None = None) -> None:
+        """Launch the plan on the current stream.  With ``timing`` (a list), a CUDA-event pair is recorded around
+        every launch and (index, start, end) is appended; read ``self.meta[index]`` for name / algorithmic work."""
+        stream = torch.cuda.current_stream().cuda_stream
+        timing = self.timing_sink if timing is None else timing
+        if timing is None:
+            for fn, args in self.calls:
+                rc = fn(*args, stream)
+                if rc != 0:
+                    raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
+            return
+        for i, (fn, args) in enumerate(self.calls):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args, stream)
+            e1.record()
+            if rc != 0:
+                raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
+            timing.append((i, e0, e1))
