@@ -1,0 +1,344 @@
+#!/usr/bin/env python
+"""Benchmark of the Seva denoising step (BASELINE.json metric: frame-steps/s, T=21 @576x576).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--T 21] [--size 72]
+
+ours       one "step" = one Euler-EDM sampler step with MultiviewCFG (CFG batch 2T) through the public
+           seva_b200.sampling / seva_b200.model API on our sm_100a kernels, 1.3 B-parameter Seva, random-init
+           weights, synthetic inputs.  `value` times K steps with everything resident in HBM; `e2e` repeats the
+           K steps with the step's inputs copied from pinned host memory and the updated latents read back
+           inside the timed region.  N > 1: one process per GPU, each rank samples its own independent T-frame
+           chunk (the two-pass procedure's second-pass chunks) - no data-path collective;
+           the timed region is bracketed by barrier + synchronize and the max over ranks is used (weak scaling).
+reference  the reference algorithm on the box's host cores: the oracle port (plain PyTorch fp32, all threads) -
+           the Python reference itself cannot travel to the GPU box - on a bounded sample of the workload.
+Prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "stable-virtual-camera_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+# Algorithmic FLOPs of the reference graph per CFG'd step (FlopCounterMode)
+REF_TFLOP_PER_STEP = {8: 26.336, 21: 76.912, 64: 314.534}
+CPU_SAMPLE_T = 2  # frames in the bounded CPU sample
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    source="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=3)
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": float(self.samples[0][1]) if self.samples else None,
+                "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------------------------------
+def build_model(device):
+    from seva_b200.model import Seva, SevaParams, SGMWrapper
+
+    params = SevaParams()
+    with torch.device("meta"):
+        m = Seva(params)
+    g = torch.Generator(device=device).manual_seed(0)
+    sd = {}
+    for k, v in m.state_dict().items():  # random-init, default PyTorch scale, generated on the device
+        if v.ndim >= 2:
+            t = (torch.rand(v.shape, device=device, generator=g) * 2 - 1) / math.sqrt(math.prod(v.shape[1:]))
+        elif k.endswith("weight"):
+            t = 1.0 + 0.1 * torch.randn(v.shape, device=device, generator=g)
+        else:
+            t = 0.05 * torch.randn(v.shape, device=device, generator=g)
+        sd[k] = t
+    m.load_state_dict(sd, assign=True)
+    return SGMWrapper(m.eval()), params
+
+
+def make_host_inputs(T, h, w, seed):
+    """Synthetic chunk in pinned host memory."""
+    from oracle import synth  # input generator only (shared with the tests); no oracle compute on this path
+    from seva_b200 import geometry as G
+
+    inp = synth.make_inputs(T, 1, h, w, lambda s, e, K, hh, ww: G.get_plucker_coordinates(s, e, K, target_size=(hh, ww)),
+                            seed=seed, num_steps=1)
+    pin = lambda t: t.contiguous().pin_memory()
+    return dict(x0=pin(inp["x0"]), c={k: pin(v) for k, v in inp["c"].items()}, uc={k: pin(v) for k, v in inp["uc"].items()},
+                c2w=pin(inp["c2w"]), K=pin(inp["K"]), mask=pin(inp["mask"]))
+
+
+def run_ours(args):
+    from seva_b200 import sampling as S
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    T, h, w = args.T, args.size, args.size
+    model, _ = build_model(dev)
+    host = make_host_inputs(T, h, w, seed=1 + rank)
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device=dev)
+    sampler = S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), num_steps=50, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
+                                s_noise=1.0, verbose=False, device=dev)
+    sigmas = disc(50, device=dev)
+    den_fn = lambda i, s, c: denoiser(model, i, s, c, num_frames=T)
+
+    def upload():
+        nb = lambda t: t.to(dev, non_blocking=True)
+        return (nb(host["x0"]), {k: nb(v) for k, v in host["c"].items()}, {k: nb(v) for k, v in host["uc"].items()},
+                nb(host["c2w"]), nb(host["K"]), nb(host["mask"]))
+
+    h2d = (host["x0"].numel() * 4 + sum(v.numel() * v.element_size() for d in (host["c"], host["uc"]) for v in d.values())
+           + host["c2w"].numel() * 4 + host["K"].numel() * 4 + host["mask"].numel())
+    d2h = host["x0"].numel() * 4
+    x_host = torch.empty_like(host["x0"]).pin_memory()
+
+    def step(i, x, c, uc, c2w, K, mask):
+        ones = x.new_ones([T])
+        k = i % 50
+        return sampler.sampler_step(ones * sigmas[k], ones * sigmas[k + 1], den_fn, x, 2.0, c, uc, 0.0, c2w=c2w, K=K,
+                                    input_frame_mask=mask)
+
+    def barrier():
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def maxed(ms):
+        if world > 1:
+            import torch.distributed as dist
+
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+        return ms
+
+    with torch.inference_mode(), torch.autocast("cuda"):
+        x, c, uc, c2w, K, mask = upload()
+        x = x * 84.9222
+        for i in range(args.warmup):
+            xw = step(i, x, c, uc, c2w, K, mask)
+        barrier()
+        eng = next(iter(model.module._engines.values()))
+        # ---- device-resident timing (value) with per-launch events on the launching stream -------
+        timing: list = []
+        eng.timing_sink = timing
+        clocks = ClockSampler(local)
+        clocks.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        xs = x
+        for i in range(args.steps):
+            xs = step(i, xs, c, uc, c2w, K, mask)
+        e1.record()
+        barrier()
+        clk = clocks.stop()
+        ms_dev = maxed(e0.elapsed_time(e1))
+        eng.timing_sink = None
+        # ---- end-to-end timing: host buffers in, host result out, every step ---------------------
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            xh, c, uc, c2w, K, mask = upload()
+            xn = step(i, xh * 84.9222, c, uc, c2w, K, mask)
+            x_host.copy_(xn, non_blocking=True)
+        e1.record()
+        barrier()
+        ms_e2e = maxed(e0.elapsed_time(e1))
+        assert torch.isfinite(x_host).all()
+
+    # ---- per-kernel aggregation from the live events -----------------------------------------------
+    agg: dict = {}
+    for idx, s0, s1 in timing:
+        name, tag, fl, nb = eng.meta[idx]
+        a = agg.setdefault(name, dict(ms=0.0, flops=0.0, bytes=0.0, n=0))
+        a["ms"] += s0.elapsed_time(s1)
+        a["flops"] += fl
+        a["bytes"] += nb
+        a["n"] += 1
+    peaks = measured_peaks()
+    plan_ms = sum(a["ms"] for a in agg.values())
+    top = max(agg.items(), key=lambda kv: kv[1]["ms"])
+    kernels = {k: dict(share=round(a["ms"] / plan_ms, 4), ms_per_step=round(a["ms"] / args.steps, 3),
+                       launches_per_step=a["n"] // args.steps,
+                       tflops=round(a["flops"] / a["ms"] / 1e9, 1) if a["flops"] and a["ms"] else None,
+                       gbs=round(a["bytes"] / a["ms"] / 1e6, 1) if a["bytes"] and a["ms"] and not a["flops"] else None)
+               for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["ms"])}
+    tname, ta = top
+    if ta["flops"]:
+        ach = ta["flops"] / ta["ms"] / 1e9
+        roof = dict(kernel=tname, bound="tensor", achieved=round(ach, 1), peak=peaks["tf_sustained"], unit="TFLOP/s",
+                    frac=round(ach / peaks["tf_sustained"], 4), traffic=None,
+                    peak_source=peaks["source"] + " sustained bf16 (kernel timed inside a long step)",
+                    launches=ta["n"], avg_launch_ms=round(ta["ms"] / ta["n"], 4),
+                    algorithmic_flops_per_launch=ta["flops"] / ta["n"])
+    else:
+        ach = ta["bytes"] / ta["ms"] / 1e6
+        roof = dict(kernel=tname, bound="hbm", achieved=round(ach, 1), peak=peaks["hbm"], unit="GB/s",
+                    frac=round(ach / peaks["hbm"], 4), traffic=None, peak_source=peaks["source"],
+                    launches=ta["n"], avg_launch_ms=round(ta["ms"] / ta["n"], 4))
+
+    if rank != 0:
+        return
+    steps = args.steps
+    value = world * T * steps / (ms_dev / 1e3)
+    e2e_v = world * T * steps / (ms_e2e / 1e3)
+    tf_step = REF_TFLOP_PER_STEP.get(T)
+    cpu = cpu_baseline(args) if world == 1 and not args.no_cpu else None
+    line = {
+        "metric": "frame-steps/s", "value": round(value, 3), "unit": "frame-steps/s", "n_gpus": world, "steps": steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_dev / steps, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"Seva 1.3B random-init, T={T} @{h * 8}x{w * 8} (latent {h}x{w}), Euler-EDM step with "
+                               f"MultiviewCFG (CFG batch {2 * T}), configs[1]",
+                   "parallelism": f"dp{world} (one independent T-frame chunk per GPU)" if world > 1 else "single GPU",
+                   "l2": "activations per step (>2 GB) exceed the 126 MB L2; no explicit flush"},
+        "e2e": {"value": round(e2e_v, 3), "unit": "frame-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": round(ms_e2e / steps, 3)},
+        "gpu_launches": eng.n_launch * steps + 4 * steps,
+        "clocks": clk, "roofline": roof,
+        "step_tflops": round(tf_step * steps / (ms_dev / 1e3), 1) if tf_step else None,
+        "step_frac_of_peak": round(tf_step * steps / (ms_dev / 1e3) / peaks["tf_sustained"], 4) if tf_step else None,
+        "kernels": kernels,
+    }
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------------------
+def cpu_step_sample(T, h, w, threads):
+    """One Euler-EDM step of the oracle port (plain PyTorch fp32) on the host cores; returns seconds."""
+    from oracle import seva_oracle as O
+    from oracle import synth
+    from seva_b200.model import Seva, SevaParams
+
+    torch.set_num_threads(threads)
+    P = SevaParams()
+    with torch.device("meta"):
+        m = Seva(P)
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    g = torch.Generator().manual_seed(0)
+    sd = {k: ((torch.rand(s, generator=g) * 2 - 1) / math.sqrt(math.prod(s[1:])) if len(s) >= 2 else
+              (torch.ones(s) if k.endswith("weight") else torch.zeros(s))) for k, s in shapes.items()}
+    inp = synth.make_inputs(T, 1, h, w, O.plucker, seed=1, num_steps=1)
+    table = O.denoiser_table()
+    fs = O.multiview_scale(2.0, 1.2, inp["c2w"], inp["K"], inp["mask"])
+    sig = torch.cat([O.ddpm_sigmas(50), torch.zeros(1)])
+    ones = torch.ones(T)
+    net = lambda x, idx, c: O.sgm_forward(sd, P, x, idx, c, num_frames=T)
+    with torch.inference_mode():
+        t0 = time.time()
+        O.sampler_step(net, table, inp["x0"] * 84.9222, ones * sig[0], ones * sig[1], fs, inp["c"], inp["uc"], inp["eps"][0])
+        return time.time() - t0
+
+
+def cpu_baseline(args):
+    threads = os.cpu_count() or 1
+    secs = cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads)
+    return {"value": round(CPU_SAMPLE_T / secs, 5), "unit": "frame-steps/s", "cores": threads, "kind": "port",
+            "sample": f"one Euler-EDM step of the oracle port (PyTorch fp32, {threads} threads) at T={CPU_SAMPLE_T} "
+                      f"@{args.size * 8}x{args.size * 8} (CFG batch {2 * CPU_SAMPLE_T}); {secs:.1f} s; per-frame cost at "
+                      f"T={args.T} is higher (3D attention grows with T^2)"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    times = []
+    for _ in range(min(args.warmup, 1)):
+        cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads)
+    for _ in range(max(1, min(args.steps, 3))):
+        times.append(cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads))
+    secs = sum(times) / len(times)
+    v = round(CPU_SAMPLE_T / secs, 5)
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    print(json.dumps({
+        "impl": "reference", "metric": "frame-steps/s", "value": v, "unit": "frame-steps/s", "n_gpus": world,
+        "steps": len(times), "warmup": min(args.warmup, 1), "ms_per_step": round(secs * 1e3, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"Seva 1.3B random-init, T={args.T} @{args.size * 8}x{args.size * 8}, Euler-EDM step with "
+                               f"MultiviewCFG, configs[1]; each step is a bounded sample (T={CPU_SAMPLE_T} frames)"},
+        "cpu_baseline": {"value": v, "unit": "frame-steps/s", "cores": threads, "kind": "port",
+                         "sample": f"oracle port (PyTorch fp32) one Euler-EDM step at T={CPU_SAMPLE_T}, {secs:.1f} s/step"},
+        "e2e": {"value": v, "unit": "frame-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--T", type=int, default=21)
+    ap.add_argument("--size", type=int, default=72)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py --impl ours needs a B200: the product path has no CPU fallback")
+        run_ours(a)

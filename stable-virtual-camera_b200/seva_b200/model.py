@@ -227,11 +227,14 @@ class Seva(nn.Module):
         eng = self._engines.get(key)
         if eng is None:
             ops.check_device()
-            if self._packed is None:
-                self._packed = pack_weights(self)
-            if len(self._engines) >= 2:  # plans own GBs of workspace: keep the two most recent shapes
-                self._engines.pop(next(iter(self._engines)))
-            eng = Engine(self, self._packed, n, num_frames, h, w, ctx_len)
+            # workspaces / packed weights must be ordinary tensors even when the caller is inside
+            # torch.inference_mode() (eval.py:1242): they are updated in place on every call
+            with torch.inference_mode(False), torch.no_grad(), torch.cuda.device(dev):
+                if self._packed is None:
+                    self._packed = pack_weights(self)
+                if len(self._engines) >= 2:  # plans own GBs of workspace: keep the two most recent shapes
+                    self._engines.pop(next(iter(self._engines)))
+                eng = Engine(self, self._packed, n, num_frames, h, w, ctx_len)
             self._engines[key] = eng
         return eng
 
