@@ -122,7 +122,10 @@ add_noise_kernel(const float* __restrict__ x, const float* __restrict__ eps, con
   if (i >= total) return;
   const int t = (int)(i / per_frame);
   const float sh = sigma_hat[t], sg = sigma[t];
-  out[i] = x[i] + eps[i] * sqrtf(sh * sh - sg * sg);
+  // separately rounded squares like the reference's `sigma_hat**2 - sigma**2` (an FMA-contracted
+  // sh*sh - sg*sg can go slightly negative when sigma_hat == sigma in fp32 and make sqrt return NaN)
+  const float var = fmaxf(__fsub_rn(__fmul_rn(sh, sh), __fmul_rn(sg, sg)), 0.0f);
+  out[i] = x[i] + eps[i] * sqrtf(var);
 }
 
 // sigma -> nearest table index (first minimum of |sigma - table|, sampling.py:126-128), quantised sigma,

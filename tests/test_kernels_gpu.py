@@ -336,6 +336,14 @@ def test_sampler_elementwise(ops):
     noise = torch.randn_like(x)
     xa = ops.add_noise(x, noise, sn, sh)
     assert torch.allclose(xa, x + noise * ((sh ** 2 - sn ** 2) ** 0.5)[:, None, None, None], rtol=1e-5, atol=1e-5)
+    # sigma_hat == sigma in fp32 for large sigma (sigma + 1e-6 rounds back): the injected noise must be exactly 0
+    from oracle import seva_oracle as O
+    sig50 = O.ddpm_sigmas(50).cuda()
+    for s in sig50[:10]:
+        sg = torch.full((T,), float(s), device="cuda")
+        xa = ops.add_noise(x, noise, sg, sg + 1e-6)
+        ref = x + noise * (((sg + 1e-6) ** 2 - sg ** 2) ** 0.5)[:, None, None, None]
+        assert torch.isfinite(xa).all() and torch.allclose(xa, ref, rtol=1e-6, atol=1e-6)
     # NCHW pack / unpack
     src = torch.randn(3, 11, h, w, device="cuda", generator=g)
     dst = torch.empty(3 * (h + 2) * (w + 2), 64, device="cuda", dtype=torch.bfloat16)
