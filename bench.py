@@ -215,6 +215,12 @@ def run_ours(args):
         a["flops"] += fl
         a["bytes"] += nb
         a["n"] += 1
+    if args.dump_launches and rank == 0:
+        rows = [dict(i=idx, name=eng.meta[idx][0], tag=eng.meta[idx][1], flops=eng.meta[idx][2], bytes=eng.meta[idx][3],
+                     ms=s0.elapsed_time(s1)) for idx, s0, s1 in timing]
+        os.makedirs(os.path.dirname(os.path.abspath(args.dump_launches)), exist_ok=True)
+        with open(args.dump_launches, "w") as f:
+            json.dump(rows, f)
     peaks = measured_peaks()
     plan_ms = sum(a["ms"] for a in agg.values())
     top = max(agg.items(), key=lambda kv: kv[1]["ms"])
@@ -335,6 +341,7 @@ if __name__ == "__main__":
     ap.add_argument("--T", type=int, default=21)
     ap.add_argument("--size", type=int, default=72)
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--dump-launches", default=None, help="write per-launch CUDA-event timings (JSON) here")
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)
