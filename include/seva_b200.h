@@ -26,7 +26,7 @@
  *   seva_upsample2x_pad       F.interpolate(scale_factor=2, mode="nearest"), layers.py:44
  *   seva_im2col3x3_s2         Downsample's stride-2 3x3 conv gather, layers.py:54-58
  *   seva_timestep_embedding   seva/modules/layers.py:11-32
- *   seva_gemv_rows            small-M Linear (time_embed, emb_layers, cross-attention with one context token)
+ *   seva_gemv_rows/_grouped   small-M Linear (time_embed, emb_layers, cross-attention with one context token)
  */
 #ifndef SEVA_B200_H_
 #define SEVA_B200_H_
@@ -176,6 +176,18 @@ int seva_timestep_embedding(const int64_t* t, float* out, int32_t N, int32_t dim
  * silu_in: apply SiLU to x first.  silu_out: apply SiLU to the result. */
 int seva_gemv_rows(const float* x, const void* W, const float* bias, float* out, int32_t M,
                    int32_t N, int32_t K, int32_t silu_in, int32_t silu_out, void* stream);
+
+/* Grouped form of seva_gemv_rows: `count` independent problems described by a table in DEVICE memory
+ * (K multiple of 8; every problem's M, N, K bounded by max_M, max_N, max_K). */
+typedef struct SevaGemvProblem {
+  const float* x;     /* fp32 [M, K] */
+  const void* W;      /* bf16 [N, K] */
+  const float* bias;  /* fp32 [N] or NULL */
+  float* out;         /* fp32 [M, N] */
+  int32_t M, N, K, silu_in, silu_out, pad_;
+} SevaGemvProblem;
+int seva_gemv_grouped(const SevaGemvProblem* problems_dev, int32_t count, int32_t max_M, int32_t max_N,
+                      int32_t max_K, void* stream);
 
 #ifdef __cplusplus
 }

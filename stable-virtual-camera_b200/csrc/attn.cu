@@ -32,6 +32,119 @@ struct AttnArgs {
   float scale_log2;
 };
 
+// ---- packed fp32x2 helpers (FFMA2 / FADD2 on sm_100) ------------------------------------------
+__device__ __forceinline__ unsigned long long pack2f(float lo, float hi) {
+  return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ unsigned long long ffma2(unsigned long long a, unsigned long long b,
+                                                    unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long fadd2(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+template <bool kTail>
+__device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], int col0, int kv_valid, float mx) {
+  float m0 = mx, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+  for (int t = 0; t < 32; t += 4) {
+    if (!kTail || col0 + t + 0 < kv_valid) m0 = fmaxf(m0, __uint_as_float(v[t + 0]));
+    if (!kTail || col0 + t + 1 < kv_valid) m1 = fmaxf(m1, __uint_as_float(v[t + 1]));
+    if (!kTail || col0 + t + 2 < kv_valid) m2 = fmaxf(m2, __uint_as_float(v[t + 2]));
+    if (!kTail || col0 + t + 3 < kv_valid) m3 = fmaxf(m3, __uint_as_float(v[t + 3]));
+  }
+  return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+}
+
+// P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; returns the partial row sum
+template <bool kTail>
+__device__ __forceinline__ void chunk_exp(const uint32_t (&v)[32], int col0, int kv_valid,
+                                          unsigned long long sl2_2, unsigned long long negm_2,
+                                          uint32_t (&pk)[16], unsigned long long& sum2) {
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const unsigned long long x2 =
+        ffma2((unsigned long long)v[2 * t] | ((unsigned long long)v[2 * t + 1] << 32), sl2_2, negm_2);
+    float p0 = fast_exp2(__uint_as_float((uint32_t)x2));
+    float p1 = fast_exp2(__uint_as_float((uint32_t)(x2 >> 32)));
+    if (kTail) {
+      if (col0 + 2 * t >= kv_valid) p0 = 0.0f;
+      if (col0 + 2 * t + 1 >= kv_valid) p1 = 0.0f;
+    }
+    sum2 = fadd2(sum2, pack2f(p0, p1));
+    pk[t] = pack_bf16x2(p0, p1);
+  }
+}
+
+// Online-softmax update for one 128x128 S tile of this thread's row: row max (pass 1), lazy O rescale,
+// P = exp2(.) written over the first 64 columns of S (pass 2).  TMEM loads are issued one chunk ahead.
+template <bool kTail>
+__device__ __forceinline__ void softmax_tile(uint32_t tS, uint32_t tO, float sl2, int kv_valid, int j,
+                                             float& m_run, float& l_run) {
+  uint32_t va[32], vb[32];
+  // ---- pass 1: row max
+  tmem_ld32(tS, va);
+  tmem_ld32(tS + 32, vb);
+  tmem_wait_ld();
+  float mx = chunk_max<kTail>(va, 0, kv_valid, -INFINITY);
+  tmem_ld32(tS + 64, va);
+  mx = chunk_max<kTail>(vb, 32, kv_valid, mx);
+  tmem_ld32(tS + 96, vb);
+  tmem_wait_ld();
+  mx = chunk_max<kTail>(va, 64, kv_valid, mx);
+  // start pass 2's first load before finishing pass 1's last reduction
+  tmem_ld32(tS, va);
+  mx = chunk_max<kTail>(vb, 96, kv_valid, mx);
+
+  const float m_new = fmaxf(m_run, mx * sl2);
+  if (j == 0) {
+    m_run = m_new;
+  } else {
+    const bool need = m_new > m_run + 8.0f;
+    if (__any_sync(0xffffffffu, need)) {
+      tmem_wait_ld();
+      const float alpha = fast_exp2(m_run - m_new);
+      l_run *= alpha;
+      m_run = m_new;
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        tmem_ld32(tO + c * 32, vb);
+        tmem_wait_ld();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) vb[t] = __float_as_uint(__uint_as_float(vb[t]) * alpha);
+        tmem_st32(tO + c * 32, vb);
+      }
+    }
+  }
+  // ---- pass 2: P = exp2(s*scale_log2 - m_run) as packed bf16 over S columns [0, 64)
+  const unsigned long long sl2_2 = pack2f(sl2, sl2);
+  const unsigned long long negm_2 = pack2f(-m_run, -m_run);
+  unsigned long long sum2 = 0ull;
+  uint32_t pk[16];
+  tmem_wait_ld();                       // chunk 0 in va
+  tmem_ld32(tS + 32, vb);               // prefetch chunk 1
+  chunk_exp<kTail>(va, 0, kv_valid, sl2_2, negm_2, pk, sum2);
+  tmem_wait_ld();                       // chunk 1 in vb (chunk 0 fully consumed)
+  tmem_st16(tS, pk);                    // P cols [0,16) overlap only S chunk 0
+  tmem_ld32(tS + 64, va);               // prefetch chunk 2
+  chunk_exp<kTail>(vb, 32, kv_valid, sl2_2, negm_2, pk, sum2);
+  tmem_wait_ld();
+  tmem_st16(tS + 16, pk);               // cols [16,32): S chunk 0, consumed
+  tmem_ld32(tS + 96, vb);               // prefetch chunk 3
+  chunk_exp<kTail>(va, 64, kv_valid, sl2_2, negm_2, pk, sum2);
+  tmem_wait_ld();
+  tmem_st16(tS + 32, pk);               // cols [32,48): S chunk 1, consumed
+  chunk_exp<kTail>(vb, 96, kv_valid, sl2_2, negm_2, pk, sum2);
+  tmem_st16(tS + 48, pk);               // cols [48,64): S chunk 1, consumed
+  l_run += __uint_as_float((uint32_t)sum2) + __uint_as_float((uint32_t)(sum2 >> 32));
+}
+
+
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -172,64 +285,10 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       mbar_wait(bar_s + 8 * i, j & 1);
       tc_fence_after();
       const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
-      // pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tS + c * 32, v);
-        tmem_wait_ld();
-        if (kv_valid >= 128) {
-#pragma unroll
-          for (int t = 0; t < 32; ++t) mx = fmaxf(mx, __uint_as_float(v[t]));
-        } else {
-#pragma unroll
-          for (int t = 0; t < 32; ++t)
-            if (c * 32 + t < kv_valid) mx = fmaxf(mx, __uint_as_float(v[t]));
-        }
-      }
-      const float m_new = fmaxf(m_run, mx * sl2);
-      if (j == 0) {
-        m_run = m_new;
-      } else {
-        const bool need = m_new > m_run + 8.0f;
-        if (__any_sync(0xffffffffu, need)) {
-          const float alpha = fast_exp2(m_run - m_new);
-          l_run *= alpha;
-          m_run = m_new;
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            uint32_t v[32];
-            tmem_ld32(tO + c * 32, v);
-            tmem_wait_ld();
-#pragma unroll
-            for (int t = 0; t < 32; ++t) v[t] = __float_as_uint(__uint_as_float(v[t]) * alpha);
-            tmem_st32(tO + c * 32, v);
-          }
-        }
-      }
-      // pass 2: P = exp2(s*scale_log2 - m_run), packed bf16 into the first 64 columns of S_i
-      float lsum = 0.0f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld32(tS + c * 32, v);
-        tmem_wait_ld();
-        uint32_t pk[16];
-#pragma unroll
-        for (int t = 0; t < 16; ++t) {
-          float p0 = fast_exp2(fmaf(__uint_as_float(v[2 * t]), sl2, -m_run));
-          float p1 = fast_exp2(fmaf(__uint_as_float(v[2 * t + 1]), sl2, -m_run));
-          if (kv_valid < 128) {
-            if (c * 32 + 2 * t >= kv_valid) p0 = 0.0f;
-            if (c * 32 + 2 * t + 1 >= kv_valid) p1 = 0.0f;
-          }
-          lsum += p0 + p1;
-          pk[t] = pack_bf16x2(p0, p1);
-        }
-        tmem_st16(tS + c * 16, pk);
-      }
-      l_run += lsum;
+      if (kv_valid >= 128)
+        softmax_tile<false>(tS, tO, sl2, 128, j, m_run, l_run);
+      else
+        softmax_tile<true>(tS, tO, sl2, kv_valid, j, m_run, l_run);
       tmem_wait_st();
       tc_fence_before();
       mbar_arrive(bar_p + 8 * i);

@@ -437,54 +437,91 @@ timestep_embedding_kernel(const long long* __restrict__ t, float* __restrict__ o
   if ((dim & 1) && k == 0) out[(long long)n * dim + dim - 1] = 0.f;
 }
 
-// out[m, n] = act(x[m, :]) . W[n, :] + bias[n]; 8 rows per block (x staged in smem), one warp per column
+// out[m, n] = act(x[m, :]) . W[n, :] + bias[n]; 8 rows per block (x staged in smem), 64 columns per block.
+// Grouped form: blockIdx.z selects one of `count` independent problems (descriptor table in device memory),
+// so the ~90 tiny per-step GEMVs (time-embedding projections, single-token cross-attention) are 3 launches.
 constexpr int kGemvRows = 8;
+constexpr int kGemvColsPerWarp = 8;
+
+__device__ __forceinline__ void gemv_tile(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
+                                          const float* __restrict__ bias, float* __restrict__ out, int M, int N,
+                                          int K, int silu_in, int silu_out, float* xs) {
+  const int m0 = blockIdx.y * kGemvRows;
+  if (m0 >= M || (int)blockIdx.x * (8 * kGemvColsPerWarp) >= N) return;
+  const int rows = min(kGemvRows, M - m0);
+  const int K4 = K >> 2;
+  const float4* x4 = reinterpret_cast<const float4*>(x + (long long)m0 * K);
+  float4* xs4 = reinterpret_cast<float4*>(xs);
+#pragma unroll 4
+  for (int i = threadIdx.x; i < kGemvRows * K4; i += blockDim.x) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < rows * K4) {
+      v = __ldg(x4 + i);
+      if (silu_in) {
+        v.x = v.x / (1.0f + __expf(-v.x));
+        v.y = v.y / (1.0f + __expf(-v.y));
+        v.z = v.z / (1.0f + __expf(-v.z));
+        v.w = v.w / (1.0f + __expf(-v.w));
+      }
+    }
+    xs4[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll 1
+  for (int cc = 0; cc < kGemvColsPerWarp; ++cc) {
+    const int n = blockIdx.x * (8 * kGemvColsPerWarp) + warp * kGemvColsPerWarp + cc;
+    if (n >= N) break;
+    float acc[kGemvRows];
+#pragma unroll
+    for (int r = 0; r < kGemvRows; ++r) acc[r] = 0.f;
+    const __nv_bfloat16* wr = W + (long long)n * K;
+    for (int k = lane * 8; k < K; k += 256) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(wr + k));
+      const float wv[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                           bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+#pragma unroll
+      for (int r = 0; r < kGemvRows; ++r) {
+        const float4 x0 = *reinterpret_cast<const float4*>(xs + r * K + k);
+        const float4 x1 = *reinterpret_cast<const float4*>(xs + r * K + k + 4);
+        acc[r] = fmaf(wv[0], x0.x, acc[r]);
+        acc[r] = fmaf(wv[1], x0.y, acc[r]);
+        acc[r] = fmaf(wv[2], x0.z, acc[r]);
+        acc[r] = fmaf(wv[3], x0.w, acc[r]);
+        acc[r] = fmaf(wv[4], x1.x, acc[r]);
+        acc[r] = fmaf(wv[5], x1.y, acc[r]);
+        acc[r] = fmaf(wv[6], x1.z, acc[r]);
+        acc[r] = fmaf(wv[7], x1.w, acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < kGemvRows; ++r) {
+      float v = acc[r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && r < rows) {
+        if (bias != nullptr) v += bias[n];
+        if (silu_out) v = v / (1.0f + __expf(-v));
+        out[(long long)(m0 + r) * N + n] = v;
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
 gemv_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
                  const float* __restrict__ bias, float* __restrict__ out, int M, int N, int K, int silu_in,
                  int silu_out) {
   extern __shared__ float xs[];  // [kGemvRows][K]
-  const int m0 = blockIdx.y * kGemvRows;
-  const int rows = min(kGemvRows, M - m0);
-  for (int i = threadIdx.x; i < kGemvRows * K; i += blockDim.x) {
-    const int r = i / K, k = i - r * K;
-    float v = 0.f;
-    if (r < rows) {
-      v = x[(long long)(m0 + r) * K + k];
-      if (silu_in) v = v / (1.0f + __expf(-v));
-    }
-    xs[i] = v;
-  }
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n = blockIdx.x * 8 + warp;
-  if (n >= N) return;
-  float acc[kGemvRows];
-#pragma unroll
-  for (int r = 0; r < kGemvRows; ++r) acc[r] = 0.f;
-  const __nv_bfloat16* wr = W + (long long)n * K;
-  for (int k = lane * 8; k < K; k += 256) {
-    const uint4 u = __ldg(reinterpret_cast<const uint4*>(wr + k));
-    const float wv[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
-                         bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
-#pragma unroll
-    for (int r = 0; r < kGemvRows; ++r) {
-      const float* xr = xs + r * K + k;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[r] = fmaf(wv[j], xr[j], acc[r]);
-    }
-  }
-#pragma unroll
-  for (int r = 0; r < kGemvRows; ++r) {
-    float v = acc[r];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0 && r < rows) {
-      if (bias != nullptr) v += bias[n];
-      if (silu_out) v = v / (1.0f + __expf(-v));
-      out[(long long)(m0 + r) * N + n] = v;
-    }
-  }
+  gemv_tile(x, W, bias, out, M, N, K, silu_in, silu_out, xs);
+}
+
+__global__ void __launch_bounds__(256)
+gemv_grouped_kernel(const SevaGemvProblem* __restrict__ probs) {
+  extern __shared__ float xs[];
+  const SevaGemvProblem p = probs[blockIdx.z];
+  gemv_tile(p.x, reinterpret_cast<const __nv_bfloat16*>(p.W), p.bias, p.out, p.M, p.N, p.K, p.silu_in,
+            p.silu_out, xs);
 }
 
 inline unsigned blocks_for(long long total, int threads) {
@@ -692,9 +729,27 @@ extern "C" int seva_gemv_rows(const float* x, const void* W, const float* bias, 
                                    200 * 1024));
     smem_set = 200 * 1024;
   }
-  dim3 grid((N + 7) / 8, (M + kGemvRows - 1) / kGemvRows);
+  dim3 grid((N + 8 * kGemvColsPerWarp - 1) / (8 * kGemvColsPerWarp), (M + kGemvRows - 1) / kGemvRows);
   gemv_rows_kernel<<<grid, 256, smem, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M,
                                                 N, K, silu_in, silu_out);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int seva_gemv_grouped(const SevaGemvProblem* problems_dev, int32_t count, int32_t max_M, int32_t max_N,
+                                 int32_t max_K, void* stream_v) {
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(problems_dev && count > 0 && max_M > 0 && max_N > 0 && max_K > 0, "seva_gemv_grouped: bad arguments");
+  SEVA_CHECK((max_K % 8) == 0 && max_K * kGemvRows * 4 <= 200 * 1024, "seva_gemv_grouped: K must be a multiple of 8 and <= 6400");
+  const size_t smem = sizeof(float) * kGemvRows * max_K;
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    SEVA_CUDA(cudaFuncSetAttribute(gemv_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    smem_set = 200 * 1024;
+  }
+  dim3 grid((max_N + 8 * kGemvColsPerWarp - 1) / (8 * kGemvColsPerWarp), (max_M + kGemvRows - 1) / kGemvRows, count);
+  gemv_grouped_kernel<<<grid, 256, smem, stream>>>(problems_dev);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

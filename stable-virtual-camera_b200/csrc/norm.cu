@@ -14,18 +14,18 @@ namespace {
 // GroupNorm statistics: per (image, channel) sum / sum of squares, fp32, atomically merged.
 // Thread owns a fixed 8-channel vector and walks rows; zero border rows of padded images add 0.
 // ------------------------------------------------------------------------------------------------
-constexpr int kStatRowsPerBlock = 128;
 
 __global__ void __launch_bounds__(512)
-gn_stats_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rpi, int C, float* sums) {
+gn_stats_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rpi, int C, float* sums,
+                int rows_per_block) {
   extern __shared__ float red[];  // [blockDim.x][16]
   const int CV = C >> 3;
   const int cv = threadIdx.x % CV;
   const int r0 = threadIdx.x / CV;
   const int RPB = blockDim.x / CV;
   const int n = blockIdx.y;
-  const int row_begin = blockIdx.x * kStatRowsPerBlock;
-  const int row_end = min(rpi, row_begin + kStatRowsPerBlock);
+  const int row_begin = blockIdx.x * rows_per_block;
+  const int row_end = min(rpi, row_begin + rows_per_block);
   float s[8], q[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.0f;
@@ -71,7 +71,6 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rpi, int
 // Thread owns a fixed 4-channel group (8-byte accesses, 256 B per warp) and walks pixels, so the
 // per-channel affine and the 4x2x7 dense weights stay in registers.
 // ------------------------------------------------------------------------------------------------
-constexpr int kApplyPixPerBlock = 96;
 
 struct GNApplyArgs {
   const __nv_bfloat16* x;
@@ -83,13 +82,13 @@ struct GNApplyArgs {
   const float* beta;
   int H, W, C, groups;
   float eps;
-  int in_padded, out_padded, silu;
+  int in_padded, out_padded, silu, pix_per_block;
   const float* dense;
   const float* dense_w;
   const float* dense_b;
 };
 
-template <bool kDense>
+template <bool kDense, int VEC>
 __global__ void __launch_bounds__(640)
 gn_apply_kernel(const GNApplyArgs a) {
   extern __shared__ float gstat[];  // [groups][2] mean, rstd
@@ -113,14 +112,14 @@ gn_apply_kernel(const GNApplyArgs a) {
   }
   __syncthreads();
 
-  const int CG = a.C >> 2;
+  const int CG = a.C / VEC;
   const int cg = threadIdx.x % CG;
   const int pl = threadIdx.x / CG;
   const int PPB = blockDim.x / CG;
-  const int c0 = cg * 4;
-  float sa[4], sb[4];
+  const int c0 = cg * VEC;
+  float sa[VEC], sb[VEC];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < VEC; ++i) {
     const int c = c0 + i;
     const int g = c / cpg;
     const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
@@ -128,10 +127,10 @@ gn_apply_kernel(const GNApplyArgs a) {
     sa[i] = rstd * ga;
     sb[i] = fmaf(-mean, rstd * ga, be);
   }
-  float ws[4][6], wh[4][6], bs[4], bh[4];
+  float ws[kDense ? VEC : 1][6], wh[kDense ? VEC : 1][6], bs[kDense ? VEC : 1], bh[kDense ? VEC : 1];
   if (kDense) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < VEC; ++i) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
         ws[i][k] = a.dense_w[(long long)(c0 + i) * 6 + k];
@@ -142,8 +141,8 @@ gn_apply_kernel(const GNApplyArgs a) {
     }
   }
 
-  const int p_begin = blockIdx.x * kApplyPixPerBlock;
-  const int p_end = min(HW, p_begin + kApplyPixPerBlock);
+  const int p_begin = blockIdx.x * a.pix_per_block;
+  const int p_end = min(HW, p_begin + a.pix_per_block);
   const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
   const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
 #pragma unroll 2
@@ -153,8 +152,20 @@ gn_apply_kernel(const GNApplyArgs a) {
     const long long prow = (long long)(yy + 1) * Wp + xx + 1;
     const long long in_row = in_img + (a.in_padded ? prow : (long long)p);
     const long long out_row = out_img + (a.out_padded ? prow : (long long)p);
-    const uint2 u = __ldg(reinterpret_cast<const uint2*>(a.x + in_row * a.ldx + c0));
-    float v[4] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y)};
+    uint32_t w[VEC / 2];
+    if (VEC == 8) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(a.x + in_row * a.ldx + c0));
+      w[0] = u.x; w[1] = u.y; w[VEC / 2 - 2] = u.z; w[VEC / 2 - 1] = u.w;
+    } else {
+      const uint2 u = __ldg(reinterpret_cast<const uint2*>(a.x + in_row * a.ldx + c0));
+      w[0] = u.x; w[1] = u.y;
+    }
+    float v[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC / 2; ++i) {
+      v[2 * i] = bf16_lo(w[i]);
+      v[2 * i + 1] = bf16_hi(w[i]);
+    }
     float pk[6];
     if (kDense) {
       const float2* dp = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p) * 6);
@@ -162,7 +173,7 @@ gn_apply_kernel(const GNApplyArgs a) {
       pk[0] = d0.x; pk[1] = d0.y; pk[2] = d1.x; pk[3] = d1.y; pk[4] = d2.x; pk[5] = d2.y;
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < VEC; ++i) {
       float h = fmaf(v[i], sa[i], sb[i]);
       if (a.silu) h = silu_f(h);
       if (kDense) {
@@ -176,10 +187,12 @@ gn_apply_kernel(const GNApplyArgs a) {
       }
       v[i] = h;
     }
-    uint2 o;
-    o.x = pack_bf16x2(v[0], v[1]);
-    o.y = pack_bf16x2(v[2], v[3]);
-    *reinterpret_cast<uint2*>(a.y + out_row * a.ldy + c0) = o;
+#pragma unroll
+    for (int i = 0; i < VEC / 2; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+    if (VEC == 8)
+      *reinterpret_cast<uint4*>(a.y + out_row * a.ldy + c0) = make_uint4(w[0], w[1], w[VEC / 2 - 2], w[VEC / 2 - 1]);
+    else
+      *reinterpret_cast<uint2*>(a.y + out_row * a.ldy + c0) = make_uint2(w[0], w[1]);
   }
 
   // zero border of a padded output image (first pixel-chunk block of each image)
@@ -192,7 +205,10 @@ gn_apply_kernel(const GNApplyArgs a) {
       else if (i < 2 * Wp) { yy = Hp - 1; xx = i - Wp; }
       else { const int k = i - 2 * Wp; yy = 1 + (k >> 1); xx = (k & 1) ? Wp - 1 : 0; }
       const long long row = out_img + (long long)yy * Wp + xx;
-      *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
+      if (VEC == 8)
+        *reinterpret_cast<uint4*>(a.y + row * a.ldy + c0) = make_uint4(0u, 0u, 0u, 0u);
+      else
+        *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
     }
   }
 }
@@ -287,9 +303,14 @@ extern "C" int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, in
   int rpb = 512 / CV;
   if (rpb < 1) rpb = 1;
   const int threads = CV * rpb;
-  dim3 grid((rpi + kStatRowsPerBlock - 1) / kStatRowsPerBlock, Nimg);
+  // ~4 blocks per SM over the whole batch, at least 2*rpb rows each so the per-block reduction is amortised
+  long long rows = ((long long)rpi * Nimg + (long long)sm_count() * 4 - 1) / ((long long)sm_count() * 4);
+  if (rows < 2 * rpb) rows = 2 * rpb;
+  if (rows > 2048) rows = 2048;
+  rows = (rows + rpb - 1) / rpb * rpb;
+  dim3 grid((rpi + (int)rows - 1) / (int)rows, Nimg);
   gn_stats_kernel<<<grid, threads, threads * 16 * sizeof(float), stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rpi, C, sums);
+      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rpi, C, sums, (int)rows);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
@@ -323,17 +344,28 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   a.dense = p->dense;
   a.dense_w = p->dense_w;
   a.dense_b = p->dense_b;
-  const int CG = p->C / 4;
+  // dense modulation keeps 4x2x7 weights per thread in registers -> 4-channel groups (8-byte accesses);
+  // the plain path uses 8-channel groups (16-byte accesses) when the strides allow it
+  const bool vec8 = !p->dense && (p->C % 8) == 0 && (p->ldx % 8) == 0 && (p->ldy % 8) == 0 &&
+                    (((uintptr_t)p->x | (uintptr_t)p->y) & 15) == 0;
+  const int CG = p->C / (vec8 ? 8 : 4);
   int ppb = 512 / CG;
   if (ppb < 1) ppb = 1;
   const int threads = CG * ppb;
   const int HW = p->H * p->Wd;
-  dim3 grid((HW + kApplyPixPerBlock - 1) / kApplyPixPerBlock, p->Nimg);
+  // ~3 blocks per SM over the batch; each block walks >= 4 pixel rounds so its register set-up is amortised
+  long long pix = ((long long)HW * p->Nimg + (long long)sm_count() * 3 - 1) / ((long long)sm_count() * 3);
+  if (pix < 4 * ppb) pix = 4 * ppb;
+  if (pix > HW) pix = HW;
+  a.pix_per_block = (int)pix;
+  dim3 grid((HW + a.pix_per_block - 1) / a.pix_per_block, p->Nimg);
   const size_t smem = sizeof(float) * 2 * p->groups;
   if (p->dense)
-    gn_apply_kernel<true><<<grid, threads, smem, stream>>>(a);
+    gn_apply_kernel<true, 4><<<grid, threads, smem, stream>>>(a);
+  else if (vec8)
+    gn_apply_kernel<false, 8><<<grid, threads, smem, stream>>>(a);
   else
-    gn_apply_kernel<false><<<grid, threads, smem, stream>>>(a);
+    gn_apply_kernel<false, 4><<<grid, threads, smem, stream>>>(a);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

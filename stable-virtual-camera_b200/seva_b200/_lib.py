@@ -38,6 +38,11 @@ class SevaGNApply(C.Structure):
     ]
 
 
+class SevaGemvProblem(C.Structure):
+    _fields_ = [("x", c_void_p), ("W", c_void_p), ("bias", c_void_p), ("out", c_void_p),
+                ("M", c_int), ("N", c_int), ("K", c_int), ("silu_in", c_int), ("silu_out", c_int), ("pad_", c_int)]
+
+
 # name -> argtypes (restype is always int unless listed in _RESTYPES)
 _PROTOS = {
     "seva_check_device": [],
@@ -66,6 +71,7 @@ _PROTOS = {
     "seva_im2col3x3_s2": [c_void_p, c_i64, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "seva_cast_f32_bf16": [c_void_p, c_void_p, c_i64, c_void_p],
     "seva_timestep_embedding": [c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
+    "seva_gemv_grouped": [c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "seva_gemv_rows": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p],
 }
 EXPORTED_SYMBOLS = sorted(list(_PROTOS) + ["seva_last_error"])

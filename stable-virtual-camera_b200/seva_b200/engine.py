@@ -119,6 +119,7 @@ class Engine:
         self.keep: list = []   # ctypes structs / tensors referenced by raw pointer
         self.bufs: dict = {}
         self.n_launch = 0
+        self.gemv_groups: dict = {}
         self.timing_sink: list | None = None  # set by bench.py to collect per-launch CUDA events
 
         # static inputs
@@ -204,11 +205,35 @@ class Engine:
                  nbytes=4.0 * x.shape[0] * x.shape[1], tag="layernorm")
         self.keep += [x, out]
 
-    def gemv(self, x, W, bias, out, *, silu_in=False, silu_out=False):
+    def gemv(self, x, W, bias, out, *, silu_in=False, silu_out=False, group=None):
+        """Small-M Linear.  With ``group`` the problem joins a grouped launch that is emitted once, right after
+        the time embedding (all grouped problems depend only on the step's (t, context), not on activations)."""
         M, K = x.shape
-        self.add(self.lib.seva_gemv_rows, x.data_ptr(), W.data_ptr(), None if bias is None else bias.data_ptr(),
-                 out.data_ptr(), M, W.shape[0], K, int(silu_in), int(silu_out))
         self.keep += [x, W, bias, out]
+        if group is None:
+            self.add(self.lib.seva_gemv_rows, x.data_ptr(), W.data_ptr(), None if bias is None else bias.data_ptr(),
+                     out.data_ptr(), M, W.shape[0], K, int(silu_in), int(silu_out), tag="gemv")
+            return
+        pr = _lib.SevaGemvProblem()
+        pr.x, pr.W, pr.bias, pr.out = x.data_ptr(), W.data_ptr(), None if bias is None else bias.data_ptr(), out.data_ptr()
+        pr.M, pr.N, pr.K, pr.silu_in, pr.silu_out = M, W.shape[0], K, int(silu_in), int(silu_out)
+        self.gemv_groups.setdefault(group, []).append(pr)
+
+    def _emit_gemv_groups(self, pos: int) -> None:
+        """Insert one grouped launch per dependency level at plan position ``pos``."""
+        for name in ("emb", "cross_v", "cross_o"):
+            probs = self.gemv_groups.get(name)
+            if not probs:
+                continue
+            arr = (_lib.SevaGemvProblem * len(probs))(*probs)
+            table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self.dev)
+            self.keep.append(table)
+            args = (table.data_ptr(), len(probs), max(p.M for p in probs), max(p.N for p in probs),
+                    max(p.K for p in probs))
+            self.calls.insert(pos, (self.lib.seva_gemv_grouped, args))
+            self.meta.insert(pos, ("seva_gemv_grouped", name, 0.0, 0.0))
+            self.n_launch += 1
+            pos += 1
 
     # ---- network -------------------------------------------------------------------------------
     def _build(self, model: Seva):
@@ -230,6 +255,7 @@ class Engine:
             self.add(lib.seva_resize_bilinear_ac, self.dense_in.data_ptr(), d.data_ptr(), N, p.dense_in_channels,
                      self.h, self.w, H, Wd)
             self.dense.append(d)
+        group_pos = len(self.calls)
 
         # ---- static schedule of where every block output lives (virtual skip concat) -----------
         in_blocks = list(model.input_blocks)
@@ -278,6 +304,7 @@ class Engine:
         hn = self.buf("final_n", self.rows_p(0), ch_h)
         self.gn(final_h, 0, ch_h, po["g"], po["b"], po["eps"], hn, silu=True)
         self.conv3x3(hn, 0, po["w"], po["cb"], self.eps, out_fp32=True)
+        self._emit_gemv_groups(group_pos)
 
     def _block(self, blk, x, lvl, dest, tag):
         layers = list(blk)
@@ -310,8 +337,8 @@ class Engine:
         h1 = self.buf(f"rb_h1_{l}", rp, cin)
         self.gn(x, l, cin, w["g1"], w["b1"], w["eps1"], h1, silu=True, dense=self.dense[l], dense_w=w["wd"],
                 dense_b=w["bd"])
-        emb_out = self.buf(f"rb_emb_{cout}", self.N, cout, F32)
-        self.gemv(self.emb, w["we"], w["be"], emb_out, silu_in=True)
+        emb_out = self.buf(f"rb_emb_{id(m)}", self.N, cout, F32)
+        self.gemv(self.emb, w["we"], w["be"], emb_out, silu_in=True, group="emb")
         h2 = self.buf(f"rb_h2_{l}", rp, cout)
         self.conv3x3(h1, l, w["w1"], w["cb1"], h2, rowbias=emb_out)
         h3 = self.buf(f"rb_h3_{l}", rp, cout)
@@ -349,10 +376,10 @@ class Engine:
     # attn2(x, ctx) = to_out(to_v(ctx)) for every query (transformer.py:59-74 with Lk = 1).
     def _cross_vec(self, wa, ctx_rows, C_, tag):
         R = ctx_rows.shape[0]
-        v = self.buf(f"xv_{tag}_{C_}", R, C_, F32)
-        o = self.buf(f"xo_{tag}_{C_}", R, C_, F32)
-        self.gemv(ctx_rows, wa["wv"], None, v)
-        self.gemv(v, wa["wo"], wa["bo"], o)
+        v = self.buf(f"xv_{tag}", R, C_, F32)
+        o = self.buf(f"xo_{tag}", R, C_, F32)
+        self.gemv(ctx_rows, wa["wv"], None, v, group="cross_v")
+        self.gemv(v, wa["wo"], wa["bo"], o, group="cross_o")
         return o
 
     def _ff(self, x, nrm, ff, residual, out, l, C_in, tag):
@@ -395,7 +422,7 @@ class Engine:
                  flops=4.0 * bat * heads * Lseq * Lseq * 64, tag="attn3d" if is3d else "attn2d")
         x1 = self.buf(f"tk_x1_{l}", rc, C_)
         if self.L == 1:
-            xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, "s3" if is3d else "s2")
+            xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
             self.gemm(o, w["s_attn1"]["wo"], x1, bias=w["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq)
         else:
             x1a = self.buf(f"tk_x1a_{l}", rc, C_)
@@ -415,7 +442,7 @@ class Engine:
                  tag="timemix")
         y2 = self.buf(f"tk_y2_{l}", rc, C_)
         if self.L == 1:
-            xr = self._cross_vec(w["t_attn2"], ctx0, C_, "t")
+            xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
             self.gemm(o, w["t_attn1"]["wo"], y2, bias=w["t_attn1"]["bo"], residual=y1, rowbias=xr,
                       rowbias_rpi=T * S)
         else:
