@@ -172,7 +172,7 @@ class Engine:
         m_alg = M if alg_rows is None else alg_rows
         kk = (A.shape[1] if Kc is None else Kc) if alg_k is None else alg_k
         self.add(self.lib.seva_gemm_bf16, C.byref(g), flops=2.0 * m_alg * W.shape[0] * kk * ntaps,
-                 tag="conv3x3" if ntaps == 9 else ("geglu" if geglu else "linear"))
+                 tag=("conv3x3" if ntaps == 9 else ("geglu" if geglu else "linear")) + f" M{M} N{W.shape[0]} K{kk * ntaps}")
 
     def conv3x3(self, x, l, W9, bias, out, *, rowbias=None, residual=None, out_fp32=False, alg_k=None):
         H, Wd = self.HW[l]
@@ -188,7 +188,7 @@ class Engine:
         sums = self.buf("gn_sums", self.N, 2 * C_, F32)
         act = 2.0 * self.N * H * Wd * C_
         self.add(self.lib.seva_groupnorm_stats, x.data_ptr(), x.stride(0), self.N, rpi, C_, sums.data_ptr(),
-                 nbytes=act, tag="gn_stats")
+                 nbytes=act, tag=f"gn_stats HW{H * Wd} C{C_}")
         pa = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
                                sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(),
                                n_img=self.N, H=H, Wd=Wd, Cc=C_, groups=32, eps=eps, in_padded=in_padded,
@@ -197,12 +197,12 @@ class Engine:
                                dense_w_ptr=None if dense_w is None else dense_w.data_ptr(),
                                dense_b_ptr=None if dense_b is None else dense_b.data_ptr())
         self.keep += [pa, x, out, gamma, beta, dense, dense_w, dense_b]
-        self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act, tag="gn_apply")
+        self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act, tag=f"gn_apply HW{H * Wd} C{C_} d{int(dense is not None)}")
 
     def ln(self, x, nrm, out):
         self.add(self.lib.seva_layernorm, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0),
                  nrm["g"].data_ptr(), nrm["b"].data_ptr(), x.shape[0], x.shape[1], nrm["eps"],
-                 nbytes=4.0 * x.shape[0] * x.shape[1], tag="layernorm")
+                 nbytes=4.0 * x.shape[0] * x.shape[1], tag=f"layernorm M{x.shape[0]} C{x.shape[1]}")
         self.keep += [x, out]
 
     def gemv(self, x, W, bias, out, *, silu_in=False, silu_out=False, group=None):
@@ -419,7 +419,7 @@ class Engine:
         base = qkv.data_ptr()
         self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
                  ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
-                 flops=4.0 * bat * heads * Lseq * Lseq * 64, tag="attn3d" if is3d else "attn2d")
+                 flops=4.0 * bat * heads * Lseq * Lseq * 64, tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
         x1 = self.buf(f"tk_x1_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
@@ -439,7 +439,7 @@ class Engine:
         self.gemm(a, w["t_attn1"]["wqkv"], qkv)
         self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
                  o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
-                 tag="timemix")
+                 tag=f"timemix BS{B * S} H{heads}")
         y2 = self.buf(f"tk_y2_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
