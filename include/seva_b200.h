@@ -68,6 +68,7 @@ typedef struct SevaGemm {
   int32_t mask_border; /* 1: rows are zero-bordered flat (Hp x Wp per image): border rows written as 0 */
   int32_t Hp, Wp;
   int32_t bn;          /* N tile (multiple of 32, <= 256; GEGLU: multiple of 64); 0 = choose            */
+  int32_t cluster;     /* 0 = choose; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile      */
 } SevaGemm;
 int seva_gemm_bf16(const SevaGemm* g, void* stream);
 /* N tile seva_gemm_bf16 will use for (N, geglu) when g->bn == 0 (weights for geglu are packed against it). */

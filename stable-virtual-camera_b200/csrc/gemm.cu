@@ -7,11 +7,19 @@
 // zero-bordered flat image: tap (dy, dx) of output row m is input row m + dy*Wp + dx, so the A tile of
 // every tap is an ordinary 2D TMA box at a shifted row coordinate (rows outside the tensor read as zero).
 //
-// Kernel shape: persistent, one CTA per SM, warp-specialised:
-//   warp 0      TMA producer  (A 128x64 + B BNx64 bf16 per stage, 128B swizzle, mbarrier ring)
-//   warp 1      tcgen05.mma issuer (UMMA 128 x BN x 16, fp32 accumulators in TMEM, 2 accumulator stages)
-//   warps 2-9   epilogue: tcgen05.ld -> bias / row-group bias / GEGLU / residual / border mask -> global
+// Kernel shape: persistent, warp-specialised, one CTA per SM; two variants of the same code:
+//   kCtas = 1   128 x BN tile per CTA
+//   kCtas = 2   256 x BN tile per CTA pair (cluster of 2, tcgen05 cta_group::2): each CTA stages its own
+//               128 rows of A and HALF of the BN weight rows, so the L2->SM operand traffic per MAC drops
+//               by a third at BN = 256; the leader CTA issues the MMAs, both CTAs run the epilogue on
+//               their own 128 accumulator rows.
+//   warp 0      TMA producer  (A 128x64 + B (BN/kCtas)x64 bf16 per stage, 128B swizzle, mbarrier ring)
+//   warp 1      tcgen05.mma issuer (UMMA (128*kCtas) x BN x 16, fp32 accumulators in TMEM, 2 stages)
+//   warps 2-9   epilogue: tcgen05.ld (one row per thread) -> bias / row-group bias / GEGLU -> transpose
+//               through a per-warp swizzled smem patch -> (+ residual, read coalesced) -> 16-byte stores
+//               in which four lanes cover one 64-byte row segment (full 32-byte sectors, no partial writes)
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/seva_b200.h"
 
 namespace seva {
@@ -22,8 +30,10 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kGemmThreads = 320;
 constexpr int kEpiWarps = 8;
-constexpr int kSmemBudget = 224 * 1024;  // dynamic smem requested at most (227 KB usable)
+constexpr int kSmemMax = 232448;         // 227 KB: the most dynamic smem one CTA can opt in to
 constexpr int kCtrlBytes = 1024;         // barriers + tmem pointer live in the first KB
+constexpr int kPatchBytes = 4096;        // per-epilogue-warp transpose patch: 32 rows x 128 B
+constexpr int kBiasSlotBytes = 512;      // per-epilogue-warp column constants of the current tile (128 fp32)
 constexpr int kMaxStages = 8;
 
 struct GemmArgs {
@@ -37,23 +47,50 @@ struct GemmArgs {
   void* out;
   long long ldo;
   int out_fp32, geglu, out_map, H, Wd, mask_border, Hp, Wp;
+  int dbg;
+  int fast;  // 1: bf16 output, N % 32 == 0 and 16-byte aligned pointers/strides -> coalesced epilogue
 };
 
-__device__ __forceinline__ float gelu_erf(float g) {
-  // exact-GELU via Abramowitz-Stegun 7.1.26 erf (|err| < 1.5e-7), two MUFU ops
-  const float x = g * 0.70710678118654752f;
-  const float ax = fabsf(x);
-  float t;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  p *= t;
-  const float e = fast_exp2(-ax * ax * 1.4426950408889634f);
-  const float erf_abs = fmaf(-p, e, 1.0f);
-  const float erf = copysignf(erf_abs, x);
-  return 0.5f * g * (1.0f + erf);
+// ---- GEGLU: x * gelu(g), exact (erf) GELU --------------------------------------------------------------
+// g * Phi(g) is evaluated as g * sigmoid(2 g p(g^2)) with p = c0 + c1 g^2 + c2 g^4 fitted to the erf form
+// (minimax over the real line, g^2 clamped at the vertex of p): max |error| 2.8e-5, i.e. 40x below the bf16
+// rounding of the stored product.  Two MUFU ops (ex2, rcp) and 4.5 packed-fp32 issue slots per element,
+// against 15 + 2 for a 7.1.26 erf -- the K = 320 GEGLU GEMMs are epilogue-bound otherwise.
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b,
+                                                   unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float lo2(unsigned long long v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi2(unsigned long long v) { return __uint_as_float((uint32_t)(v >> 32)); }
+
+// (x0, x1) <- (x0 * gelu(g0), x1 * gelu(g1))
+__device__ __forceinline__ void geglu2(float& x0, float& x1, float g0, float g1) {
+  constexpr float kC0 = -2.3010568618774414f;    // -2 log2(e) * 0.7974855517
+  constexpr float kC1 = -0.10683422535657883f;   // -2 log2(e) * 0.0370259212
+  constexpr float kC2 = 0.0010237497044727206f;  // -2 log2(e) * -0.000354804609
+  const unsigned long long g = pk2(g0, g1);
+  const unsigned long long gg = mul2(g, g);
+  const unsigned long long g2 = pk2(fminf(lo2(gg), 52.0f), fminf(hi2(gg), 52.0f));
+  unsigned long long p = fma2(pk2(kC2, kC2), g2, pk2(kC1, kC1));
+  p = fma2(p, g2, pk2(kC0, kC0));
+  const unsigned long long u = mul2(g, p);
+  const float e0 = fast_exp2(lo2(u)), e1 = fast_exp2(hi2(u));  // exp(-2 g p)
+  float r0, r1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(e0 + 1.0f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(e1 + 1.0f));
+  const unsigned long long o = mul2(mul2(pk2(x0, x1), g), pk2(r0, r1));
+  x0 = lo2(o);
+  x1 = hi2(o);
 }
 
 struct RowInfo {
@@ -63,7 +100,20 @@ struct RowInfo {
   int rb_group;  // row-group for rowbias
 };
 
-// Finish 32 consecutive output columns [n, n+32) of one row and store them.
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w)
+               : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 u;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+               : "r"(addr)
+               : "memory");
+  return u;
+}
+
+// ---- generic (slow) path: one row per thread straight to global; any N, fp32 or bf16 output ----------
 __device__ __forceinline__ void finish_store32(const GemmArgs& a, const RowInfo& ri, float (&f)[32],
                                                int n) {
   if (!ri.valid) return;
@@ -77,25 +127,9 @@ __device__ __forceinline__ void finish_store32(const GemmArgs& a, const RowInfo&
   }
   if (a.residual != nullptr) {
     const __nv_bfloat16* r = a.residual + ri.out_row * a.ldr + n;
-    if (ncols >= 32 && (a.ldr & 7) == 0) {
-      const uint4* r4 = reinterpret_cast<const uint4*>(r);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint4 u = __ldg(r4 + q);
-        f[q * 8 + 0] += bf16_lo(u.x);
-        f[q * 8 + 1] += bf16_hi(u.x);
-        f[q * 8 + 2] += bf16_lo(u.y);
-        f[q * 8 + 3] += bf16_hi(u.y);
-        f[q * 8 + 4] += bf16_lo(u.z);
-        f[q * 8 + 5] += bf16_hi(u.z);
-        f[q * 8 + 6] += bf16_lo(u.w);
-        f[q * 8 + 7] += bf16_hi(u.w);
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) f[j] += __bfloat162float(r[j]);
-    }
+    for (int j = 0; j < 32; ++j)
+      if (j < ncols) f[j] += __bfloat162float(r[j]);
   }
   if (ri.border) {
 #pragma unroll
@@ -103,37 +137,90 @@ __device__ __forceinline__ void finish_store32(const GemmArgs& a, const RowInfo&
   }
   if (a.out_fp32) {
     float* o = reinterpret_cast<float*>(a.out) + ri.out_row * a.ldo + n;
-    if (ncols >= 32 && (a.ldo & 3) == 0) {
-      float4* o4 = reinterpret_cast<float4*>(o);
 #pragma unroll
-      for (int q = 0; q < 8; ++q)
-        o4[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) o[j] = f[j];
-    }
+    for (int j = 0; j < 32; ++j)
+      if (j < ncols) o[j] = f[j];
   } else {
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(a.out) + ri.out_row * a.ldo + n;
-    if (ncols >= 32 && (a.ldo & 7) == 0) {
-      uint4* o4 = reinterpret_cast<uint4*>(o);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 u;
-        u.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
-        u.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
-        u.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
-        u.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
-        o4[q] = u;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) o[j] = __float2bfloat16(f[j]);
-    }
+    for (int j = 0; j < 32; ++j)
+      if (j < ncols) o[j] = __float2bfloat16(f[j]);
   }
 }
 
+// ---- fast path ------------------------------------------------------------------------------------------
+// tinfo[i] describes tile row 8*i + lane/4 of this warp's 32 rows: -1 = skip, else out_row | border << 30.
+// Lane (r, p = lane & 3) of the transposed view owns columns [8p, 8p+8) of the 32-column chunk.
+// No residual: pack to bf16 in the row-per-thread view, transpose 32 rows x 64 B, store.
+__device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t patch, int lane,
+                                                 const int (&tinfo)[4], const float (&f)[32], int border,
+                                                 int n) {
+  {
+    const uint32_t row = patch + lane * 64;
+    const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t w0 = pack_bf16x2(f[8 * q + 0], f[8 * q + 1]);
+      uint32_t w1 = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+      uint32_t w2 = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+      uint32_t w3 = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+      if (border) w0 = w1 = w2 = w3 = 0u;
+      sts128(row + ((q ^ sw) << 4), w0, w1, w2, w3);
+    }
+  }
+  __syncwarp();
+  const int p = lane & 3;
+  __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(a.out) + n + p * 8;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = 8 * i + (lane >> 2);
+    const uint4 u = lds128(patch + r * 64 + ((p ^ ((r >> 1) & 3)) << 4));
+    if (tinfo[i] >= 0)
+      *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u;
+  }
+  __syncwarp();
+}
+
+// Residual: transpose the fp32 values (32 rows x 128 B), add the bf16 residual read with the same
+// coalesced mapping (already in registers: issued before the TMEM load), round once, store.
+__device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patch, int lane,
+                                                const int (&tinfo)[4], const float (&f)[32],
+                                                const uint4 (&res)[4], int n) {
+  {
+    const uint32_t row = patch + lane * 128;
+    const uint32_t sw = lane & 7;
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      sts128(row + ((q ^ sw) << 4), __float_as_uint(f[4 * q]), __float_as_uint(f[4 * q + 1]),
+             __float_as_uint(f[4 * q + 2]), __float_as_uint(f[4 * q + 3]));
+  }
+  __syncwarp();
+  const int p = lane & 3;
+  __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(a.out) + n + p * 8;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = 8 * i + (lane >> 2);
+    const uint32_t rowa = patch + r * 128;
+    const uint4 lo = lds128(rowa + (((2 * p) ^ (r & 7)) << 4));
+    const uint4 hi = lds128(rowa + (((2 * p + 1) ^ (r & 7)) << 4));
+    if (tinfo[i] >= 0) {
+      uint4 u;
+      if (tinfo[i] & 0x40000000) {
+        u = make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        const uint4 rr = res[i];
+        u.x = pack_bf16x2(__uint_as_float(lo.x) + bf16_lo(rr.x), __uint_as_float(lo.y) + bf16_hi(rr.x));
+        u.y = pack_bf16x2(__uint_as_float(lo.z) + bf16_lo(rr.y), __uint_as_float(lo.w) + bf16_hi(rr.y));
+        u.z = pack_bf16x2(__uint_as_float(hi.x) + bf16_lo(rr.z), __uint_as_float(hi.y) + bf16_hi(rr.z));
+        u.w = pack_bf16x2(__uint_as_float(hi.z) + bf16_lo(rr.w), __uint_as_float(hi.w) + bf16_hi(rr.w));
+      }
+      *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u;
+    }
+  }
+  __syncwarp();
+}
+
+template <int kCtas>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const GemmArgs a) {
@@ -145,13 +232,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t bar_tfull = smem_base + 16 * kMaxStages;   // 2 x 8 B
   const uint32_t bar_tempty = bar_tfull + 16;               // 2 x 8 B
   const uint32_t tmem_slot = bar_tempty + 16;               // 4 B
-  const uint32_t tiles_base = smem_base + kCtrlBytes;
+  const uint32_t patch_base = smem_base + kCtrlBytes;       // kEpiWarps x kPatchBytes
+  const uint32_t bias_base = patch_base + kEpiWarps * kPatchBytes;   // kEpiWarps x kBiasSlotBytes
+  const uint32_t tiles_base = bias_base + kEpiWarps * kBiasSlotBytes;
   const uint32_t a_bytes = BM * BK * 2;
-  const uint32_t b_bytes = a.bn * BK * 2;
+  const uint32_t b_rows = a.bn / kCtas;
+  const uint32_t b_bytes = b_rows * BK * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = kCtas == 2 ? cluster_ctarank() : 0u;
+  const int cluster_id = blockIdx.x / kCtas;
+  const int n_clusters = gridDim.x / kCtas;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -162,13 +255,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
-      mbar_init(bar_tempty + 8 * s, kEpiWarps);
+      mbar_init(bar_tempty + 8 * s, kEpiWarps * kCtas);
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) {
+    if (kCtas == 2) tmem_alloc_pair(tmem_slot, 512);
+    else tmem_alloc(tmem_slot, 512);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kCtas == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
@@ -176,72 +273,152 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int iters = a.ntaps * a.kchunks;
 
   if (warp == 0) {
-    // ------------------------------- TMA producer -------------------------------------------
-    if (lane == 0) {
-      uint32_t it_g = 0;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / a.n_tiles) * BM;
-        const int n0 = (tile % a.n_tiles) * a.bn;
-        for (int it = 0; it < iters; ++it, ++it_g) {
-          const uint32_t s = it_g % a.stages;
-          const uint32_t ph = (it_g / a.stages) & 1;
-          const int tap = it / a.kchunks;
-          const int kc = it - tap * a.kchunks;
+    // ------------------------------- TMA producer (every CTA) -------------------------------
+    {   // all 32 lanes run the (warp-uniform) loop so that addresses stay in uniform registers;
+        // one elected lane issues the TMA instructions
+      uint32_t it_g = 0, s = 0, ph = 0;
+      for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters) {
+        const int m0 = (tile / a.n_tiles) * (BM * kCtas) + rank * BM;
+        const int n0 = (tile % a.n_tiles) * a.bn + rank * b_rows;
+        for (int tap = 0; tap < a.ntaps; ++tap) {
           int off = 0;
           if (a.ntaps == 9) off = (tap / 3 - 1) * a.tap_wp + (tap % 3 - 1);
-          mbar_wait(bar_empty + 8 * s, ph ^ 1);
-          mbar_expect_tx(bar_full + 8 * s, stage_bytes);
-          const uint32_t sa = tiles_base + s * stage_bytes;
-          tma_load_2d(sa, &tmA, bar_full + 8 * s, kc * BK, m0 + off);
-          tma_load_2d(sa + a_bytes, &tmB, bar_full + 8 * s, tap * a.Kc + kc * BK, n0);
+          for (int kc = 0; kc < a.kchunks; ++kc, ++it_g) {
+            mbar_wait(bar_empty + 8 * s, ph ^ 1);
+            const uint32_t sa = tiles_base + s * stage_bytes;
+            if (elect_one()) {
+              if ((a.dbg & 1) && it_g >= (uint32_t)a.stages) {
+                if (rank == 0) mbar_arrive(bar_full + 8 * s);
+              } else if (kCtas == 2) {
+                // both CTAs' bytes are counted on the leader's barrier (the MMA issuer waits there)
+                const uint32_t fb = mapa_cluster(bar_full + 8 * s, 0);
+                if (rank == 0) mbar_expect_tx(bar_full + 8 * s, stage_bytes * 2);
+                tma_load_2d_pair(sa, &tmA, fb, kc * BK, m0 + off);
+                tma_load_2d_pair(sa + a_bytes, &tmB, fb, tap * a.Kc + kc * BK, n0);
+              } else {
+                mbar_expect_tx(bar_full + 8 * s, stage_bytes);
+                tma_load_2d(sa, &tmA, bar_full + 8 * s, kc * BK, m0 + off);
+                tma_load_2d(sa + a_bytes, &tmB, bar_full + 8 * s, tap * a.Kc + kc * BK, n0);
+              }
+            }
+            __syncwarp();
+            if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
+          }
         }
+      }
+      // tail: do not leave while MMA-completion arrivals for this CTA's slots are still in flight
+      const uint32_t pend = it_g < (uint32_t)a.stages ? it_g : (uint32_t)a.stages;
+      for (uint32_t j = 0; j < pend; ++j) {
+        // slot s is the oldest outstanding one; its release completes the phase the next fill would wait for
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------- MMA issuer ----------------------------------------------
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(BM, a.bn, 0, 0);
-      uint32_t it_g = 0, tl = 0;
-      for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++tl) {
+    // ------------------------------- MMA issuer (leader CTA) ---------------------------------
+    if (rank == 0) {   // whole warp loops (uniform); one elected lane issues
+      const uint32_t idesc = make_idesc_bf16(BM * kCtas, a.bn, 0, 0);
+      uint32_t tl = 0, s = 0, ph = 0;
+      for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
         const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
         mbar_wait(bar_tempty + 8 * as, aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * 256;
-        for (int it = 0; it < iters; ++it, ++it_g) {
-          const uint32_t s = it_g % a.stages;
-          const uint32_t ph = (it_g / a.stages) & 1;
-          mbar_wait(bar_full + 8 * s, ph);
+        for (int it = 0; it < iters; ++it) {
+          if (!(a.dbg & 4)) mbar_wait(bar_full + 8 * s, ph);
           tc_fence_after();
           const uint32_t sa = tiles_base + s * stage_bytes;
           const uint64_t adesc = make_sdesc_sw128(sa, 16, 1024);
           const uint64_t bdesc = make_sdesc_sw128(sa + a_bytes, 16, 1024);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            // advance 16 bf16 (32 B) along K inside the 128B swizzle row: +2 in the >>4 address field
-            umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              // advance 16 bf16 (32 B) along K inside the 128B swizzle row: +2 in the >>4 address field
+              if (kCtas == 2)
+                umma_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0 ? 1u : 0u);
+              else
+                umma_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0 ? 1u : 0u);
+            }
+            if (kCtas == 2) tc_commit_pair(bar_empty + 8 * s);
+            else tc_commit(bar_empty + 8 * s);
           }
-          tc_commit(bar_empty + 8 * s);
+          __syncwarp();
+          if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1; }
         }
-        tc_commit(bar_tfull + 8 * as);
+        if (elect_one()) {
+          if (kCtas == 2) tc_commit_pair(bar_tfull + 8 * as);
+          else tc_commit(bar_tfull + 8 * as);
+        }
+        __syncwarp();
       }
     }
   } else {
-    // ------------------------------- epilogue --------------------------------------------------
+    // ------------------------------- epilogue (every CTA) ---------------------------------------
+    const int ew = warp - 2;
     const int quarter = warp & 3;        // TMEM lane quarter this warp may access
-    const int half = (warp - 2) >> 2;    // which half of the tile's columns
+    const int half = ew >> 2;            // which half of the tile's columns
     const int row_in_tile = quarter * 32 + lane;
+    const uint32_t patch = patch_base + ew * kPatchBytes;
+    const uint32_t bslot = bias_base + ew * kBiasSlotBytes;
+    // accumulator columns this warp drains: [seg_lo, seg_lo + seg_len), for GEGLU also the gate twin at + bn/2
+    const int nunits = a.geglu ? a.bn / 64 : a.bn / 32;
+    const int u_begin = half == 0 ? 0 : (nunits + 1) / 2;
+    const int u_end = half == 0 ? (nunits + 1) / 2 : nunits;
+    const int seg_lo = u_begin * 32, seg_len = (u_end - u_begin) * 32;
+    const bool has_cb = a.fast && (a.bias != nullptr || a.rowbias != nullptr);
+
+    // Column-bias staging: lane L fetches 4 of the (at most 128) per-column constants this warp needs for a
+    // tile -- bias[n] (+ rowbias[g0][n], g0 = row group of the warp's first row) -- one tile ahead; they are
+    // parked in the warp's smem slot at the top of the tile and read back as broadcast LDS.128.
+    auto fetch_cb = [&](int tile_) -> float4 {
+      float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!has_cb || tile_ >= a.num_tiles) return r;
+      int o = 4 * lane, twin = 0;
+      if (a.geglu && o >= 64) { o -= 64; twin = a.bn / 2; }
+      if (o >= seg_len || (a.geglu && 4 * lane >= 128)) return r;
+      const int n = (tile_ % a.n_tiles) * a.bn + seg_lo + o + twin;
+      if (n >= a.N) return r;
+      if (a.bias != nullptr) r = __ldg(reinterpret_cast<const float4*>(a.bias + n));
+      if (a.rowbias != nullptr) {
+        int mf = (tile_ / a.n_tiles) * (BM * kCtas) + rank * BM + quarter * 32;
+        if (mf > a.M - 1) mf = a.M - 1;
+        const float4 q = __ldg(reinterpret_cast<const float4*>(
+            a.rowbias + (long long)(mf / a.rowbias_rpi) * a.Nout + n));
+        r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
+      }
+      return r;
+    };
+    auto add_slot32 = [&](uint32_t saddr, float (&f)[32]) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint4 b = lds128(saddr + 16 * q);
+        f[4 * q + 0] += __uint_as_float(b.x);
+        f[4 * q + 1] += __uint_as_float(b.y);
+        f[4 * q + 2] += __uint_as_float(b.z);
+        f[4 * q + 3] += __uint_as_float(b.w);
+      }
+    };
+
+    float4 cb_next = fetch_cb(cluster_id);
     uint32_t tl = 0;
-    for (int tile = blockIdx.x; tile < a.num_tiles; tile += gridDim.x, ++tl) {
+    for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
       const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
       const int tile_n = tile % a.n_tiles;
-      const int m0 = (tile / a.n_tiles) * BM;
+      const int m0 = (tile / a.n_tiles) * (BM * kCtas) + rank * BM;
       const int n0 = tile_n * a.bn;
       const int m = m0 + row_in_tile;
+      if (has_cb) {
+        sts128(bslot + 16 * lane, __float_as_uint(cb_next.x), __float_as_uint(cb_next.y),
+               __float_as_uint(cb_next.z), __float_as_uint(cb_next.w));
+        __syncwarp();
+        cb_next = fetch_cb(tile + n_clusters);
+      }
       RowInfo ri;
       ri.valid = m < a.M;
       ri.border = 0;
       ri.out_row = m;
       ri.rb_group = 0;
+      int rb_fix = 0;  // this row's group differs from the staged one (tile straddles two row groups)
       if (ri.valid) {
         if (a.out_map == 1) {
           const int hw = a.H * a.Wd;
@@ -257,68 +434,128 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int x = r - y * a.Wp;
           ri.border = (y == 0) | (y == a.Hp - 1) | (x == 0) | (x == a.Wp - 1);
         }
-        if (a.rowbias != nullptr) ri.rb_group = m / a.rowbias_rpi;
+        if (a.rowbias != nullptr) {
+          ri.rb_group = m / a.rowbias_rpi;
+          int mf = m0 + quarter * 32;
+          if (mf > a.M - 1) mf = a.M - 1;
+          rb_fix = ri.rb_group != mf / a.rowbias_rpi;
+        }
+      }
+      int tinfo[4];
+      {
+        const int info = ri.valid ? ((int)ri.out_row | (ri.border << 30)) : -1;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tinfo[i] = __shfl_sync(0xffffffffu, info, 8 * i + (lane >> 2));
       }
 
-      mbar_wait(bar_tfull + 8 * as, aph);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + as * 256 + (uint32_t(quarter * 32) << 16);
+      // release of this accumulator stage: after this warp's last TMEM load of the tile
+      auto release_tmem = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (kCtas == 2 && rank != 0) mbar_arrive_cluster(mapa_cluster(bar_tempty + 8 * as, 0));
+          else mbar_arrive(bar_tempty + 8 * as);
+        }
+      };
 
-      if (!a.geglu) {
-        const int nchunks = a.bn / 32;
-        const int c_begin = half == 0 ? 0 : (nchunks + 1) / 2;
-        const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
-        for (int c = c_begin; c < c_end; ++c) {
+      if (u_begin >= u_end) {
+        mbar_wait(bar_tfull + 8 * as, aph);
+        release_tmem();
+      } else if (!a.geglu) {
+        for (int c = u_begin; c < u_end; ++c) {
+          const int n = n0 + c * 32;
+          const bool live = n < a.N;  // whole chunk beyond N on the tile tail (uniform)
+          uint4 res[4];
+          if (a.fast && a.residual != nullptr && live) {
+            const __nv_bfloat16* rbase = a.residual + n + (lane & 3) * 8;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              res[i] = make_uint4(0u, 0u, 0u, 0u);
+              if (tinfo[i] >= 0)
+                res[i] = __ldg(reinterpret_cast<const uint4*>(rbase + (long long)(tinfo[i] & 0x3fffffff) * a.ldr));
+            }
+          }
+          if (c == u_begin) {
+            mbar_wait(bar_tfull + 8 * as, aph);
+            tc_fence_after();
+          }
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_wait_ld();
+          if (c == u_end - 1) release_tmem();
+          if (!live || (a.dbg & 2)) continue;
           float f[32];
-          const int n = n0 + c * 32;
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if (a.bias != nullptr) {
+          if (a.fast) {
+            if (has_cb) add_slot32(bslot + (c - u_begin) * 128, f);
+            if (rb_fix) {  // rare: rows of two row groups in one warp tile
+              const float* r1 = a.rowbias + (long long)ri.rb_group * a.Nout + n;
+              int mf = m0 + quarter * 32;
+              if (mf > a.M - 1) mf = a.M - 1;
+              const float* r0 = a.rowbias + (long long)(mf / a.rowbias_rpi) * a.Nout + n;
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (n + j < a.N) f[j] += __ldg(a.bias + n + j);
+              for (int j = 0; j < 32; ++j) f[j] += __ldg(r1 + j) - __ldg(r0 + j);
+            }
+            if (a.residual != nullptr) store_chunk_res(a, patch, lane, tinfo, f, res, n);
+            else store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n);
+          } else {
+            if (a.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (n + j < a.N) f[j] += __ldg(a.bias + n + j);
+            }
+            finish_store32(a, ri, f, n);
           }
-          finish_store32(a, ri, f, n);
         }
       } else {
-        const int npairs = a.bn / 64;
-        const int p_begin = half == 0 ? 0 : (npairs + 1) / 2;
-        const int p_end = half == 0 ? (npairs + 1) / 2 : npairs;
-        for (int p = p_begin; p < p_end; ++p) {
+        mbar_wait(bar_tfull + 8 * as, aph);
+        tc_fence_after();
+        for (int p = u_begin; p < u_end; ++p) {
           uint32_t vx[32], vg[32];
           tmem_ld32(taddr + p * 32, vx);
           tmem_ld32(taddr + a.bn / 2 + p * 32, vg);
           tmem_wait_ld();
-          float f[32];
-          const int nx = n0 + p * 32;
-          const int ng = n0 + a.bn / 2 + p * 32;
+          if (p == u_end - 1) release_tmem();
+          if (a.dbg & 2) continue;
+          float f[32], g[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
-            float xv = __uint_as_float(vx[j]);
-            float gv = __uint_as_float(vg[j]);
-            if (a.bias != nullptr) {
-              xv += __ldg(a.bias + nx + j);
-              gv += __ldg(a.bias + ng + j);
-            }
-            f[j] = xv * gelu_erf(gv);
+            f[j] = __uint_as_float(vx[j]);
+            g[j] = __uint_as_float(vg[j]);
           }
-          finish_store32(a, ri, f, tile_n * (a.bn / 2) + p * 32);
+          if (a.fast) {
+            if (has_cb) {
+              add_slot32(bslot + (p - u_begin) * 128, f);
+              add_slot32(bslot + 256 + (p - u_begin) * 128, g);
+            }
+          } else if (a.bias != nullptr) {
+            const int nx = n0 + p * 32;
+            const int ng = n0 + a.bn / 2 + p * 32;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              f[j] += __ldg(a.bias + nx + j);
+              g[j] += __ldg(a.bias + ng + j);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) geglu2(f[j], f[j + 1], g[j], g[j + 1]);
+          const int n_out = tile_n * (a.bn / 2) + p * 32;
+          if (a.fast) store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n_out);
+          else finish_store32(a, ri, f, n_out);
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (kCtas == 2) cluster_sync_all();
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (kCtas == 2) tmem_dealloc_pair(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -365,6 +602,7 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   SEVA_CHECK(!(g->out_map == 1) || (g->H > 0 && g->Wd > 0), "seva_gemm_bf16: out_map=1 needs H, Wd");
   SEVA_CHECK(!g->mask_border || (g->Hp > 2 && g->Wp > 2), "seva_gemm_bf16: mask_border needs Hp, Wp");
   SEVA_CHECK(g->rowbias == nullptr || g->rowbias_rpi > 0, "seva_gemm_bf16: rowbias_rpi must be > 0");
+  SEVA_CHECK(g->cluster >= 0 && g->cluster <= 2, "seva_gemm_bf16: cluster must be 0 (auto), 1 or 2");
 
   GemmArgs a;
   a.M = g->M;
@@ -376,12 +614,6 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.kchunks = (g->Kc + BK - 1) / BK;
   a.bn = bn;
   a.n_tiles = (g->N + bn - 1) / bn;
-  const int m_tiles = (g->M + BM - 1) / BM;
-  a.num_tiles = m_tiles * a.n_tiles;
-  const int stage_bytes = BM * BK * 2 + bn * BK * 2;
-  int stages = (kSmemBudget - kCtrlBytes - 1024) / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
-  a.stages = stages;
   a.bias = g->bias;
   a.rowbias = g->rowbias;
   a.rowbias_rpi = g->rowbias_rpi;
@@ -397,6 +629,30 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.mask_border = g->mask_border;
   a.Hp = g->Hp;
   a.Wp = g->Wp;
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  {
+    static int dbg = -1;
+    if (dbg < 0) { const char* e = getenv("SEVA_GEMM_DEBUG"); dbg = e ? atoi(e) : 0; }
+    a.dbg = dbg;
+  }
+  a.fast = !g->out_fp32 && (a.Nout % 32) == 0 && (g->N % 32) == 0 && (g->ldo % 8) == 0 && al16(g->out) &&
+           (g->bias == nullptr || al16(g->bias)) && (g->rowbias == nullptr || al16(g->rowbias)) &&
+           (g->residual == nullptr || ((g->ldr % 8) == 0 && al16(g->residual)));
+
+  // CTA pair (256-row tiles, half the weight rows per CTA) once the main loop is long enough for the operand
+  // traffic to matter (measured cross-over: K*taps around 1024); short-K problems are epilogue/HBM-bound and
+  // keep the finer 128-row granularity.
+  const int sms = sm_count();
+  int ctas = g->cluster;
+  if (ctas == 0) ctas = ((long long)g->ntaps * g->Kc >= 1024 && g->M > BM) ? 2 : 1;
+  const int m_tiles = (g->M + BM * ctas - 1) / (BM * ctas);
+  a.num_tiles = m_tiles * a.n_tiles;
+  const int b_rows = bn / ctas;
+  const int stage_bytes = BM * BK * 2 + b_rows * BK * 2;
+  const int fixed = kCtrlBytes + 1024 + kEpiWarps * (kPatchBytes + kBiasSlotBytes);
+  int stages = (kSmemMax - fixed) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  a.stages = stages;
 
   CUtensorMap tmA, tmB;
   {
@@ -408,20 +664,38 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   {
     const uint64_t dims[2] = {(uint64_t)g->ntaps * g->Kc, (uint64_t)g->N};
     const uint64_t strides[1] = {(uint64_t)g->ldw * 2};
-    const uint32_t box[2] = {BK, (uint32_t)bn};
+    const uint32_t box[2] = {BK, (uint32_t)b_rows};
     if (make_tmap_bf16(&tmB, g->W, 2, dims, strides, box)) return 4;
   }
 
-  const int smem = kCtrlBytes + 1024 + stages * stage_bytes;
+  const int smem = fixed + stages * stage_bytes;
   static bool attr_set = false;
   if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   kSmemBudget));
+    SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
+    SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
     attr_set = true;
   }
-  int grid = sm_count();
-  if (grid > a.num_tiles) grid = a.num_tiles;
-  gemm_kernel<<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
+  if (ctas == 1) {
+    int grid = sms;
+    if (grid > a.num_tiles) grid = a.num_tiles;
+    gemm_kernel<1><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
+  } else {
+    int pairs = sms / 2;
+    if (pairs > a.num_tiles) pairs = a.num_tiles;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2>, tmA, tmB, a));
+  }
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

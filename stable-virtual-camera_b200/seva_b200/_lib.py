@@ -24,7 +24,7 @@ class SevaGemm(C.Structure):
         ("residual", c_void_p), ("ldr", c_i64),
         ("out", c_void_p), ("ldo", c_i64),
         ("out_fp32", c_int), ("geglu", c_int), ("out_map", c_int), ("H", c_int), ("Wd", c_int),
-        ("mask_border", c_int), ("Hp", c_int), ("Wp", c_int), ("bn", c_int),
+        ("mask_border", c_int), ("Hp", c_int), ("Wp", c_int), ("bn", c_int), ("cluster", c_int),
     ]
 
 

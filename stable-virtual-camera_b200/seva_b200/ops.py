@@ -43,7 +43,7 @@ def pick_bn(N: int, geglu: bool = False) -> int:
 # ------------------------------------------------------------------------------------------------
 def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1, tap_wp=0, bias_ptr=None,
               rowbias_ptr=None, rowbias_rpi=0, residual_ptr=None, ldr=0, out_fp32=False, geglu=False,
-              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0) -> SevaGemm:
+              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, cluster=0) -> SevaGemm:
     g = SevaGemm()
     g.A, g.lda, g.a_rows = A_ptr, lda, a_rows
     g.W, g.ldw = W_ptr, ldw
@@ -52,7 +52,7 @@ def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1
     g.residual, g.ldr = residual_ptr, ldr
     g.out, g.ldo = out_ptr, ldo
     g.out_fp32, g.geglu, g.out_map, g.H, g.Wd = int(out_fp32), int(geglu), out_map, H, Wd
-    g.mask_border, g.Hp, g.Wp, g.bn = int(mask_border), Hp, Wp, bn
+    g.mask_border, g.Hp, g.Wp, g.bn, g.cluster = int(mask_border), Hp, Wp, bn, cluster
     return g
 
 
@@ -62,7 +62,7 @@ def run_gemm(g: SevaGemm) -> None:
 
 def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *, out: torch.Tensor | None = None,
            residual: torch.Tensor | None = None, rowbias: torch.Tensor | None = None, rowbias_rpi: int = 0,
-           geglu: bool = False, out_fp32: bool = False, bn: int = 0) -> torch.Tensor:
+           geglu: bool = False, out_fp32: bool = False, bn: int = 0, cluster: int = 0) -> torch.Tensor:
     """out = A @ W.T (+bias) (+rowbias[row // rpi]) (+residual); A [M,K] bf16, W [N,K] bf16 (row strides free)."""
     _req(A, torch.bfloat16, "A"), _req(W, torch.bfloat16, "W")
     M, K = A.shape
@@ -73,14 +73,16 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *
     g = make_gemm(A_ptr=A.data_ptr(), lda=A.stride(0), a_rows=M, W_ptr=W.data_ptr(), ldw=W.stride(0), M=M, N=N,
                   Kc=K, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias), rowbias_ptr=_p(rowbias),
                   rowbias_rpi=rowbias_rpi, residual_ptr=_p(residual),
-                  ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, geglu=geglu, bn=bn)
+                  ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, geglu=geglu, bn=bn,
+                  cluster=cluster)
     run_gemm(g)
     return out
 
 
 def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None, N_img: int, H: int, Wd: int, *,
                    out: torch.Tensor | None = None, residual: torch.Tensor | None = None,
-                   rowbias: torch.Tensor | None = None, out_fp32: bool = False, bn: int = 0) -> torch.Tensor:
+                   rowbias: torch.Tensor | None = None, out_fp32: bool = False, bn: int = 0,
+                   cluster: int = 0) -> torch.Tensor:
     """3x3/s1/p1 conv on a zero-bordered flat image x [N_img*(H+2)*(Wd+2), Cin]; W9 [Cout, 9*Cin] tap-major."""
     _req(x, torch.bfloat16, "x"), _req(W9, torch.bfloat16, "W9")
     rows, Cin = x.shape
@@ -93,7 +95,7 @@ def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None,
                   N=Cout, Kc=Cin, ntaps=9, tap_wp=Wp, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias),
                   rowbias_ptr=_p(rowbias), rowbias_rpi=Hp * Wp, residual_ptr=_p(residual),
                   ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, mask_border=True,
-                  Hp=Hp, Wp=Wp, bn=bn)
+                  Hp=Hp, Wp=Wp, bn=bn, cluster=cluster)
     run_gemm(g)
     return out
 

@@ -81,6 +81,56 @@ def test_gemm_geglu(ops, M, K, inner):
     assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
 
 
+@pytest.mark.parametrize("cluster", [1, 2])
+@pytest.mark.parametrize("M,K,N", [(130, 64, 32), (257, 320, 320), (1000, 640, 960), (4097, 1280, 256), (77, 128, 2560)])
+def test_gemm_cluster_modes(ops, cluster, M, K, N):
+    """Both tile shapes of seva_gemm_bf16 (one CTA per 128 rows / CTA pair per 256 rows) with bias, row-group bias
+    and residual through the coalesced epilogue, ragged M and strided output."""
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + K + N + cluster)
+    A = bf(torch.randn(M, K, device="cuda", generator=g))
+    W = bf(torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K))
+    b = torch.randn(N, device="cuda", generator=g)
+    res = bf(torch.randn(M, N, device="cuda", generator=g))
+    rpi = 61
+    rb = torch.randn((M + rpi - 1) // rpi, N, device="cuda", generator=g)
+    outbuf = torch.full((M + 3, N + 16), 7.0, device="cuda", dtype=torch.bfloat16)
+    out = ops.linear(A, W, b, out=outbuf[:M, 16:], residual=res, rowbias=rb, rowbias_rpi=rpi, cluster=cluster)
+    rows = torch.arange(M, device="cuda") // rpi
+    ref = A.float() @ W.float().t() + b + res.float() + rb[rows]
+    assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
+    assert (outbuf[:, :16] == 7).all() and (outbuf[M:] == 7).all()  # nothing written outside the view
+    out2 = ops.linear(A, W, None, cluster=cluster)
+    assert rel_l2(out2, A.float() @ W.float().t()) < 5e-3
+
+
+@pytest.mark.parametrize("cluster", [1, 2])
+def test_gemm_geglu_and_conv_cluster_modes(ops, cluster):
+    from seva_b200 import pack
+
+    g = torch.Generator(device="cuda").manual_seed(100 + cluster)
+    M, K, inner = 700, 320, 1280
+    A = bf(torch.randn(M, K, device="cuda", generator=g))
+    W = bf(torch.randn(2 * inner, K, device="cuda", generator=g) / math.sqrt(K))
+    b = torch.randn(2 * inner, device="cuda", generator=g) * 0.1
+    Wp, bp = pack.pack_geglu(W, b, ops.pick_bn(2 * inner, True))
+    out = ops.linear(A, Wp, bp, geglu=True, cluster=cluster)
+    x, gate = (A.float() @ W.float().t() + b).chunk(2, dim=-1)
+    assert rel_l2(out, x * F.gelu(gate)) < 5e-3
+    n_img, H, Wd, Cin, Cout = 3, 18, 10, 128, 320
+    x = bf(torch.randn(n_img, Cin, H, Wd, device="cuda", generator=g))
+    w = torch.randn(Cout, Cin, 3, 3, device="cuda", generator=g) / math.sqrt(9 * Cin)
+    bb = torch.randn(Cout, device="cuda", generator=g)
+    xp = F.pad(x.permute(0, 2, 3, 1), (0, 0, 1, 1, 1, 1)).reshape(-1, Cin).contiguous()
+    res = F.pad(bf(torch.randn(n_img, H, Wd, Cout, device="cuda", generator=g)), (0, 0, 1, 1, 1, 1)).reshape(-1, Cout).contiguous()
+    rb = torch.randn(n_img, Cout, device="cuda", generator=g)
+    o = ops.conv3x3_padded(xp, pack.pack_conv3x3(w), bb, n_img, H, Wd, rowbias=rb, residual=res, cluster=cluster)
+    o = o.reshape(n_img, H + 2, Wd + 2, Cout)
+    ref = F.conv2d(x.float(), bf(w).float(), bb, padding=1) + rb[:, :, None, None]
+    ref = ref.permute(0, 2, 3, 1) + res.reshape(n_img, H + 2, Wd + 2, Cout)[:, 1:-1, 1:-1].float()
+    assert o[:, 0].abs().max() == 0 and o[:, -1].abs().max() == 0 and o[:, :, 0].abs().max() == 0 and o[:, :, -1].abs().max() == 0
+    assert rel_l2(o[:, 1:-1, 1:-1], ref) < 5e-3
+
+
 @pytest.mark.parametrize("n_img,H,Wd,Cin,Cout", [(2, 9, 9, 64, 64), (3, 18, 18, 128, 320), (2, 36, 20, 320, 640),
                                                  (1, 72, 72, 64, 320)])
 def test_conv3x3(ops, n_img, H, Wd, Cin, Cout):

@@ -14,6 +14,8 @@ from seva_b200 import ops, pack
 dev = "cuda"
 flush = torch.empty(256 * 1024 * 1024, device=dev, dtype=torch.uint8)
 filt = sys.argv[1] if len(sys.argv) > 1 else ""
+CL = int(os.environ.get("SEVA_CLUSTER", "0"))
+BN = int(os.environ.get("SEVA_BN", "0"))
 
 
 def timeit(fn, n=5):
@@ -55,11 +57,11 @@ for kind, M, N, K, has_res in LIN:
         bn = ops.pick_bn(N, True)
         Wp, bp = pack.pack_geglu(W, b, bn)
         out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
-        fn = lambda: ops.linear(A, Wp, bp, geglu=True, out=out)
+        fn = lambda: ops.linear(A, Wp, bp, geglu=True, out=out, cluster=CL)
     else:
         res = rnd(M, N).bfloat16() if has_res else None
         out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-        fn = lambda: ops.linear(A, W, b, out=out, residual=res)
+        fn = lambda: ops.linear(A, W, b, out=out, residual=res, cluster=CL, bn=BN)
     t = timeit(fn)
     def ref(rows):
         y = A[rows].float() @ W.float().t() + b
@@ -91,7 +93,7 @@ for n_img, H, Cin, Cout, has_res in CONV:
         rimg[:, 1:-1, 1:-1] = rnd(n_img, H, H, Cout)
         res = rimg.reshape(-1, Cout).bfloat16()
     out = torch.empty(n_img * Hp * Hp, Cout, device=dev, dtype=torch.bfloat16)
-    fn = lambda: ops.conv3x3_padded(x, W9, b, n_img, H, H, out=out, residual=res)
+    fn = lambda: ops.conv3x3_padded(x, W9, b, n_img, H, H, out=out, residual=res, cluster=CL, bn=BN)
     t = timeit(fn)
     xi = x.reshape(n_img, Hp, Hp, Cin)[:2, 1:-1, 1:-1].permute(0, 3, 1, 2).float()
     y = F.conv2d(xi, Wc.float(), b, padding=1).permute(0, 2, 3, 1)
