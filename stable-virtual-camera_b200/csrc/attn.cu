@@ -192,63 +192,70 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 
   if (warp == 0) {
     // ------------------------------------ TMA producer -----------------------------------------
-    if (lane == 0) {
+    // all lanes run the loop (addresses stay warp-uniform / in uniform registers); one elected lane issues
+    if (elect_one()) {
       mbar_expect_tx(bar_q, 2 * kTileBytes);
       tma_load_3d(q_smem, &tmQ, bar_q, head * 64, q0, b);
       tma_load_3d(q_smem + kTileBytes, &tmQ, bar_q, head * 64, q0 + 128, b);
-      for (int e = 0; e < 2 * nkv; ++e) {
-        const uint32_t s = e % kRing, ph = (e / kRing) & 1;
-        const int j = e >> 1;
-        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+    }
+    __syncwarp();
+    uint32_t s = 0, ph = 0;
+    for (int e = 0; e < 2 * nkv; ++e) {
+      const int j = e >> 1;
+      mbar_wait(bar_empty + 8 * s, ph ^ 1);
+      if (elect_one()) {
         mbar_expect_tx(bar_full + 8 * s, kTileBytes);
-        tma_load_3d(ring_smem + s * kTileBytes, (e & 1) ? &tmV : &tmK, bar_full + 8 * s, head * 64,
-                    j * 128, b);
+        tma_load_3d(ring_smem + s * kTileBytes, (e & 1) ? &tmV : &tmK, bar_full + 8 * s, head * 64, j * 128, b);
       }
+      __syncwarp();
+      if (++s == kRing) { s = 0; ph ^= 1; }
     }
   } else if (warp == 1) {
     // ------------------------------------ MMA issuer --------------------------------------------
-    if (lane == 0) {
-      const uint32_t idesc_qk = make_idesc_bf16(128, 128, 0, 0);
-      const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major (d contiguous)
-      const uint64_t qdesc0 = make_sdesc_sw128(q_smem, 16, 1024);
-      const uint64_t qdesc1 = make_sdesc_sw128(q_smem + kTileBytes, 16, 1024);
-      auto ring_wait = [&](int e) {
-        mbar_wait(bar_full + 8 * (e % kRing), (e / kRing) & 1);
-      };
-      auto ring_addr = [&](int e) { return ring_smem + (e % kRing) * kTileBytes; };
-      auto issue_s = [&](int i, int e_k) {
-        const uint64_t kdesc = make_sdesc_sw128(ring_addr(e_k), 16, 1024);
-        const uint64_t qd = i ? qdesc1 : qdesc0;
+    // whole warp runs the (uniform) schedule; one elected lane issues each group of MMAs + commits
+    const uint32_t idesc_qk = make_idesc_bf16(128, 128, 0, 0);
+    const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major (d contiguous)
+    const uint64_t qdesc0 = make_sdesc_sw128(q_smem, 16, 1024);
+    const uint64_t qdesc1 = make_sdesc_sw128(q_smem + kTileBytes, 16, 1024);
+    auto ring_wait = [&](int e) { mbar_wait(bar_full + 8 * (e % kRing), (e / kRing) & 1); };
+    auto ring_addr = [&](int e) { return ring_smem + (e % kRing) * kTileBytes; };
+    auto issue_s = [&](int i, int e_k) {
+      const uint64_t kdesc = make_sdesc_sw128(ring_addr(e_k), 16, 1024);
+      const uint64_t qd = i ? qdesc1 : qdesc0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
-      };
-      auto issue_pv = [&](int i, int e_v, int j) {
-        const uint32_t vaddr = ring_addr(e_v);
+      for (int k = 0; k < 4; ++k)
+        umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
+    };
+    auto issue_pv = [&](int i, int e_v, int j) {
+      const uint32_t vaddr = ring_addr(e_v);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart; P columns advance by 8
-          const uint64_t vdesc = make_sdesc_sw128(vaddr + k * 2048, 8192, 1024);
-          umma_ts(tmem_base + 256 + i * 64, tmem_base + i * 128 + k * 8, vdesc, idesc_pv,
-                  (j | k) != 0 ? 1u : 0u);
-        }
-      };
+      for (int k = 0; k < 8; ++k) {
+        // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart; P columns advance by 8
+        const uint64_t vdesc = make_sdesc_sw128(vaddr + k * 2048, 8192, 1024);
+        umma_ts(tmem_base + 256 + i * 64, tmem_base + i * 128 + k * 8, vdesc, idesc_pv,
+                (j | k) != 0 ? 1u : 0u);
+      }
+    };
 
-      mbar_wait(bar_q, 0);
-      ring_wait(0);
-      tc_fence_after();
+    mbar_wait(bar_q, 0);
+    ring_wait(0);
+    tc_fence_after();
+    if (elect_one()) {
       issue_s(0, 0);
       tc_commit(bar_s);
       issue_s(1, 0);
       tc_commit(bar_s + 8);
       tc_commit(bar_empty + 0);
-      for (int j = 0; j < nkv; ++j) {
-        const int e_v = 2 * j + 1, e_kn = 2 * j + 2;
-        const bool has_next = j + 1 < nkv;
-        ring_wait(e_v);
-        if (has_next) ring_wait(e_kn);
-        mbar_wait(bar_p, j & 1);
-        tc_fence_after();
+    }
+    __syncwarp();
+    for (int j = 0; j < nkv; ++j) {
+      const int e_v = 2 * j + 1, e_kn = 2 * j + 2;
+      const bool has_next = j + 1 < nkv;
+      ring_wait(e_v);
+      if (has_next) ring_wait(e_kn);
+      mbar_wait(bar_p, j & 1);
+      tc_fence_after();
+      if (elect_one()) {
         issue_pv(0, e_v, j);
         if (has_next) {
           issue_s(0, e_kn);
@@ -256,8 +263,11 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         } else {
           tc_commit(bar_o);
         }
-        mbar_wait(bar_p + 8, j & 1);
-        tc_fence_after();
+      }
+      __syncwarp();
+      mbar_wait(bar_p + 8, j & 1);
+      tc_fence_after();
+      if (elect_one()) {
         issue_pv(1, e_v, j);
         tc_commit(bar_empty + 8 * (e_v % kRing));
         if (has_next) {
@@ -268,6 +278,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           tc_commit(bar_o + 8);
         }
       }
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ------------------------------------ softmax + epilogue ------------------------------------

@@ -188,6 +188,219 @@ timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
   }
 }
 
+// ---- short frame axes (T <= 32): one warp per (b, s, head) item on the tensor cores ---------------------
+// "lane = query, K/V broadcast from smem" is bound by the LDS -> register write-back (512 B per broadcast
+// LDS.128) at about a sixth of the HBM roofline, with bf16 or fp32 staging alike (measured).  The 21x21x64
+// problem is far too small for a 128-row tcgen05 tile, so the item is padded to 32x32x64 and runs as 64
+// warp-level mma.sync.m16n8k16 (bf16 -> fp32): S = Q K^T as 2x4 accumulator tiles, softmax on the fragments
+// (quad shuffles), P re-used as the A fragment of O = P V.  Q/K/V rows (128 B each, one DRAM burst) are staged
+// through a per-warp XOR-swizzled smem patch; 16 warps per SM keep enough row loads in flight for HBM.
+constexpr int kTmmWarps = 4;
+constexpr int kTmmBytes = 3 * 4096;  // per warp: Q, K, V tiles of 32 rows x 128 B
+
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+      "{%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// byte offset of 16-byte chunk `chunk` of row `row` in a swizzled 32 x 128 B tile
+__device__ __forceinline__ uint32_t tm_off(int row, int chunk) {
+  return (uint32_t)(row * 128 + ((chunk ^ (row & 7)) << 4));
+}
+
+__global__ void __launch_bounds__(kTmmWarps * 32, 4)
+timemix_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int B, int T,
+                   int S, int Hh, long long ldqkv, long long ldo, float scale_log2, long long total,
+                   long long nwarps_total) {
+  extern __shared__ __align__(128) uint8_t tm_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t qS = smem_u32(tm_smem) + warp * kTmmBytes;
+  const uint32_t kS = qS + 4096, vS = qS + 8192;
+  const int C = Hh * 64;
+  const int sub = lane >> 3, part = lane & 7;  // staging: 8 lanes x 16 B per row, 4 rows per instruction
+  const int g = lane >> 2, q4 = lane & 3;      // fragment coordinates
+  // rows >= T stay zero for the whole kernel (V rows meet P = 0 there: they must be finite)
+  for (int i = lane; i < kTmmBytes / 16; i += 32)
+    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(qS + i * 16), "r"(0u) : "memory");
+  __syncwarp();
+
+  for (long long item = (long long)blockIdx.x * kTmmWarps + warp; item < total; item += nwarps_total) {
+    const int h = (int)(item % Hh);
+    const long long bs = item / Hh;
+    const int s = (int)(bs % S);
+    const int b = (int)(bs / S);
+    // ---- stage Q, K, V: two rounds of 16 rows, each with its 12 row loads issued before the stores
+    __syncwarp();  // the previous item's output staging has been read
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      if (half * 16 < T) {
+        uint4 lq[4], lk[4], lv[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int t = half * 16 + 4 * r + sub;
+          if (t < T) {
+            const long long row = ((long long)b * T + t) * S + s;
+            const __nv_bfloat16* base = qkv + row * ldqkv + h * 64 + part * 8;
+            lq[r] = __ldg(reinterpret_cast<const uint4*>(base));
+            lk[r] = __ldg(reinterpret_cast<const uint4*>(base + C));
+            lv[r] = __ldg(reinterpret_cast<const uint4*>(base + 2 * C));
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int t = half * 16 + 4 * r + sub;
+          if (t < T) {
+            const uint32_t o = tm_off(t, part);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(qS + o), "r"(lq[r].x), "r"(lq[r].y), "r"(lq[r].z), "r"(lq[r].w) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(kS + o), "r"(lk[r].x), "r"(lk[r].y), "r"(lk[r].z), "r"(lk[r].w) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(vS + o), "r"(lv[r].x), "r"(lv[r].y), "r"(lv[r].z), "r"(lv[r].w) : "memory");
+          }
+        }
+      }
+    }
+    __syncwarp();
+
+    // ---- S = Q K^T : [2 m-tiles][4 n-tiles] of 16x8
+    float sc[2][4][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) sc[mt][nt][i] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+      uint32_t af[2][4], bf[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) ldsm_x4(qS + tm_off(mt * 16 + (lane & 15), ks * 2 + (lane >> 4)), af[mt]);
+#pragma unroll
+      for (int np = 0; np < 2; ++np)
+        ldsm_x4(kS + tm_off(np * 16 + (lane & 7) + ((lane >> 4) << 3), ks * 2 + ((lane >> 3) & 1)), bf[np]);
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma_bf16(sc[mt][nt], af[mt], bf[nt >> 1][(nt & 1) * 2], bf[nt >> 1][(nt & 1) * 2 + 1]);
+    }
+    // ---- softmax over keys (columns); thread holds rows g, g+8 of each m-tile, columns nt*8 + 2*q4 + {0,1}
+    float inv_l[2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+      for (int hr = 0; hr < 2; ++hr) {
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int key = nt * 8 + 2 * q4 + e;
+            float v = sc[mt][nt][hr * 2 + e] * scale_log2;
+            if (key >= T) v = -INFINITY;
+            sc[mt][nt][hr * 2 + e] = v;
+            mx = fmaxf(mx, v);
+          }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        float l = 0.f;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const float pv = fast_exp2(sc[mt][nt][hr * 2 + e] - mx);
+            sc[mt][nt][hr * 2 + e] = pv;
+            l += pv;
+          }
+        l += __shfl_xor_sync(0xffffffffu, l, 1);
+        l += __shfl_xor_sync(0xffffffffu, l, 2);
+        inv_l[mt][hr] = 1.0f / l;
+      }
+    }
+    // ---- O = P V : [2 m-tiles][8 d-tiles]
+    float oc[2][8][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int dt = 0; dt < 8; ++dt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) oc[mt][dt][i] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+      uint32_t pa[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        pa[mt][0] = pack_bf16x2(sc[mt][2 * kk][0], sc[mt][2 * kk][1]);
+        pa[mt][1] = pack_bf16x2(sc[mt][2 * kk][2], sc[mt][2 * kk][3]);
+        pa[mt][2] = pack_bf16x2(sc[mt][2 * kk + 1][0], sc[mt][2 * kk + 1][1]);
+        pa[mt][3] = pack_bf16x2(sc[mt][2 * kk + 1][2], sc[mt][2 * kk + 1][3]);
+      }
+#pragma unroll
+      for (int dp = 0; dp < 4; ++dp) {
+        uint32_t vf[4];
+        ldsm_x4_trans(vS + tm_off(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), dp * 2 + (lane >> 4)), vf);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          mma_bf16(oc[mt][2 * dp], pa[mt], vf[0], vf[1]);
+          mma_bf16(oc[mt][2 * dp + 1], pa[mt], vf[2], vf[3]);
+        }
+      }
+    }
+    // ---- normalise, stage O in the Q tile (all Q reads are done), coalesced 16-byte row stores
+    __syncwarp();
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int dt = 0; dt < 8; ++dt) {
+        const int r0 = mt * 16 + g;
+        const uint32_t w0 = pack_bf16x2(oc[mt][dt][0] * inv_l[mt][0], oc[mt][dt][1] * inv_l[mt][0]);
+        const uint32_t w1 = pack_bf16x2(oc[mt][dt][2] * inv_l[mt][1], oc[mt][dt][3] * inv_l[mt][1]);
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qS + tm_off(r0, dt) + q4 * 4), "r"(w0) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qS + tm_off(r0 + 8, dt) + q4 * 4), "r"(w1) : "memory");
+      }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int t = 4 * r + sub;
+      if (t < T) {
+        uint4 u;
+        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(qS + tm_off(t, part)) : "memory");
+        const long long row = ((long long)b * T + t) * S + s;
+        *reinterpret_cast<uint4*>(out + row * ldo + h * 64 + part * 8) = u;
+      }
+    }
+    // rows >= T of the Q tile were overwritten by the padded query rows' outputs: harmless (Q rows >= T only
+    // produce rows >= T), but they must stay finite: they are bf16 of finite values.
+  }
+}
+
+int launch_timemix_mma(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int T, int S, int Hh,
+                       long long ldqkv, long long ldo, float scale_log2, cudaStream_t stream) {
+  const size_t smem = (size_t)kTmmWarps * kTmmBytes;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SEVA_CUDA(cudaFuncSetAttribute(timemix_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  const long long total = (long long)B * S * Hh;
+  long long grid = 4ll * sm_count();  // 16 warps per SM, each striding over items
+  const long long need = (total + kTmmWarps - 1) / kTmmWarps;
+  if (grid > need) grid = need;
+  timemix_mma_kernel<<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(qkv, out, B, T, S, Hh, ldqkv, ldo,
+                                                                       scale_log2, total, grid * kTmmWarps);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
 template <int TMAX>
 int launch_timemix(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int T, int S, int Hh,
                    long long ldqkv, long long ldo, float scale_log2, cudaStream_t stream) {
@@ -224,8 +437,7 @@ extern "C" int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t 
   const __nv_bfloat16* qp = reinterpret_cast<const __nv_bfloat16*>(qkv);
   __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(out);
   const float sl2 = scale * 1.4426950408889634f;
-  if (T <= 24) return launch_timemix<24>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
-  if (T <= 32) return launch_timemix<32>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
+  if (T <= 32) return launch_timemix_mma(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
   if (T <= 64) return launch_timemix<64>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
   return launch_timemix<128>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
 }
