@@ -68,8 +68,11 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int rpi, int
 
 // ------------------------------------------------------------------------------------------------
 // GroupNorm apply (+SiLU, + h*(1+scale)+shift with scale/shift = W[2C,6] p + b recomputed per pixel)
-// Thread owns a fixed 4-channel group (8-byte accesses, 256 B per warp) and walks pixels, so the
-// per-channel affine and the 4x2x7 dense weights stay in registers.
+// A thread owns a fixed channel vector (4 channels when the Plucker modulation keeps its 4x2x6 dense
+// weights in registers, else 8) and walks pixels; kUnroll row loads are issued before any is consumed so
+// that ~16 warps per SM keep >= 32 KB in flight (the first version, 2 loads deep, sat at 1.1 TB/s).  All
+// arithmetic is packed fp32x2 (FFMA2): at HBM speed the dense variant has a budget of ~21 issue slots per
+// element and needs ~15.
 // ------------------------------------------------------------------------------------------------
 
 struct GNApplyArgs {
@@ -83,13 +86,32 @@ struct GNApplyArgs {
   int H, W, C, groups;
   float eps;
   int in_padded, out_padded, silu, pix_per_block;
+  int cslice;          // channels handled per blockIdx.z
+  unsigned w_magic;    // ceil(2^32 / W): p / W == umulhi(p, w_magic) for p < 2^32 / W
   const float* dense;
   const float* dense_w;
   const float* dense_b;
 };
 
-template <bool kDense, int VEC>
-__global__ void __launch_bounds__(640)
+typedef unsigned long long f2_t;  // two packed fp32
+__device__ __forceinline__ f2_t f2(float lo, float hi) {
+  return (f2_t)__float_as_uint(lo) | ((f2_t)__float_as_uint(hi) << 32);
+}
+__device__ __forceinline__ float f2lo(f2_t v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float f2hi(f2_t v) { return __uint_as_float((uint32_t)(v >> 32)); }
+__device__ __forceinline__ f2_t f2fma(f2_t a, f2_t b, f2_t c) {
+  f2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f2_t f2mul(f2_t a, f2_t b) {
+  f2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+template <bool kDense, int VEC, int kUnroll>
+__global__ void __launch_bounds__(512)
 gn_apply_kernel(const GNApplyArgs a) {
   extern __shared__ float gstat[];  // [groups][2] mean, rstd
   const int n = blockIdx.y;
@@ -112,32 +134,40 @@ gn_apply_kernel(const GNApplyArgs a) {
   }
   __syncthreads();
 
-  const int CG = a.C / VEC;
+  constexpr int NP = VEC / 2;  // packed pairs per thread
+  const int CG = a.cslice / VEC;
   const int cg = threadIdx.x % CG;
   const int pl = threadIdx.x / CG;
   const int PPB = blockDim.x / CG;
-  const int c0 = cg * VEC;
-  float sa[VEC], sb[VEC];
+  const int c0 = blockIdx.z * a.cslice + cg * VEC;
+  f2_t sa[NP], sb[NP];
 #pragma unroll
-  for (int i = 0; i < VEC; ++i) {
-    const int c = c0 + i;
-    const int g = c / cpg;
-    const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
-    const float ga = a.gamma[c], be = a.beta[c];
-    sa[i] = rstd * ga;
-    sb[i] = fmaf(-mean, rstd * ga, be);
+  for (int i = 0; i < NP; ++i) {
+    float ta[2], tb[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * i + e;
+      const int g = c / cpg;
+      const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
+      const float ga = a.gamma[c], be = a.beta[c];
+      ta[e] = rstd * ga;
+      tb[e] = fmaf(-mean, rstd * ga, be);
+    }
+    sa[i] = f2(ta[0], ta[1]);
+    sb[i] = f2(tb[0], tb[1]);
   }
-  float ws[kDense ? VEC : 1][6], wh[kDense ? VEC : 1][6], bs[kDense ? VEC : 1], bh[kDense ? VEC : 1];
+  f2_t ws[kDense ? NP : 1][6], wh[kDense ? NP : 1][6], bs[kDense ? NP : 1], bh[kDense ? NP : 1];
   if (kDense) {
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) {
+    for (int i = 0; i < NP; ++i) {
+      const int c = c0 + 2 * i;
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
-        ws[i][k] = a.dense_w[(long long)(c0 + i) * 6 + k];
-        wh[i][k] = a.dense_w[(long long)(a.C + c0 + i) * 6 + k];
+        ws[i][k] = f2(a.dense_w[(long long)c * 6 + k], a.dense_w[(long long)(c + 1) * 6 + k]);
+        wh[i][k] = f2(a.dense_w[(long long)(a.C + c) * 6 + k], a.dense_w[(long long)(a.C + c + 1) * 6 + k]);
       }
-      bs[i] = 1.0f + a.dense_b[c0 + i];  // fold the "1 +" of h*(1+scale)
-      bh[i] = a.dense_b[a.C + c0 + i];
+      bs[i] = f2(1.0f + a.dense_b[c], 1.0f + a.dense_b[c + 1]);  // fold the "1 +" of h*(1+scale)
+      bh[i] = f2(a.dense_b[a.C + c], a.dense_b[a.C + c + 1]);
     }
   }
 
@@ -145,54 +175,65 @@ gn_apply_kernel(const GNApplyArgs a) {
   const int p_end = min(HW, p_begin + a.pix_per_block);
   const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
   const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
-#pragma unroll 2
-  for (int p = p_begin + pl; p < p_end; p += PPB) {
-    const int yy = p / a.W;
-    const int xx = p - yy * a.W;
-    const long long prow = (long long)(yy + 1) * Wp + xx + 1;
-    const long long in_row = in_img + (a.in_padded ? prow : (long long)p);
-    const long long out_row = out_img + (a.out_padded ? prow : (long long)p);
-    uint32_t w[VEC / 2];
-    if (VEC == 8) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(a.x + in_row * a.ldx + c0));
-      w[0] = u.x; w[1] = u.y; w[VEC / 2 - 2] = u.z; w[VEC / 2 - 1] = u.w;
-    } else {
-      const uint2 u = __ldg(reinterpret_cast<const uint2*>(a.x + in_row * a.ldx + c0));
-      w[0] = u.x; w[1] = u.y;
-    }
-    float v[VEC];
+  const f2_t half2 = f2(0.5f, 0.5f);
+  for (int pb = p_begin + pl; pb < p_end; pb += PPB * kUnroll) {
+    uint32_t w[kUnroll][NP];
+    int prow[kUnroll];
 #pragma unroll
-    for (int i = 0; i < VEC / 2; ++i) {
-      v[2 * i] = bf16_lo(w[i]);
-      v[2 * i + 1] = bf16_hi(w[i]);
-    }
-    float pk[6];
-    if (kDense) {
-      const float2* dp = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p) * 6);
-      const float2 d0 = __ldg(dp), d1 = __ldg(dp + 1), d2 = __ldg(dp + 2);
-      pk[0] = d0.x; pk[1] = d0.y; pk[2] = d1.x; pk[3] = d1.y; pk[4] = d2.x; pk[5] = d2.y;
-    }
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) {
-      float h = fmaf(v[i], sa[i], sb[i]);
-      if (a.silu) h = silu_f(h);
-      if (kDense) {
-        float sc = bs[i], sh = bh[i];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          sc = fmaf(ws[i][k], pk[k], sc);
-          sh = fmaf(wh[i][k], pk[k], sh);
+    for (int u = 0; u < kUnroll; ++u) {
+      const int p = pb + u * PPB;
+      if (p < p_end) {
+        const int yy = (int)__umulhi((unsigned)p, a.w_magic);
+        prow[u] = p + 2 * yy + Wp + 1;  // (yy + 1) * Wp + xx + 1
+        const long long in_row = in_img + (a.in_padded ? prow[u] : p);
+        const __nv_bfloat16* src = a.x + in_row * a.ldx + c0;
+        if (VEC == 8) {
+          const uint4 t = __ldg(reinterpret_cast<const uint4*>(src));
+          w[u][0] = t.x; w[u][1] = t.y; w[u][NP - 2] = t.z; w[u][NP - 1] = t.w;
+        } else {
+          const uint2 t = __ldg(reinterpret_cast<const uint2*>(src));
+          w[u][0] = t.x; w[u][1] = t.y;
         }
-        h = fmaf(h, sc, sh);
       }
-      v[i] = h;
     }
 #pragma unroll
-    for (int i = 0; i < VEC / 2; ++i) w[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
-    if (VEC == 8)
-      *reinterpret_cast<uint4*>(a.y + out_row * a.ldy + c0) = make_uint4(w[0], w[1], w[VEC / 2 - 2], w[VEC / 2 - 1]);
-    else
-      *reinterpret_cast<uint2*>(a.y + out_row * a.ldy + c0) = make_uint2(w[0], w[1]);
+    for (int u = 0; u < kUnroll; ++u) {
+      const int p = pb + u * PPB;
+      if (p < p_end) {
+        f2_t pk[6];
+        if (kDense) {
+          const float2* dp = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p) * 6);
+          const float2 d0 = __ldg(dp), d1 = __ldg(dp + 1), d2 = __ldg(dp + 2);
+          pk[0] = f2(d0.x, d0.x); pk[1] = f2(d0.y, d0.y); pk[2] = f2(d1.x, d1.x);
+          pk[3] = f2(d1.y, d1.y); pk[4] = f2(d2.x, d2.x); pk[5] = f2(d2.y, d2.y);
+        }
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+          f2_t h = f2fma(f2(bf16_lo(w[u][i]), bf16_hi(w[u][i])), sa[i], sb[i]);
+          if (a.silu) {  // x * sigmoid(x), sigmoid(x) = 0.5 * tanh(0.5 x) + 0.5
+            const f2_t hh = f2mul(h, half2);
+            const f2_t t = f2(fast_tanh(f2lo(hh)), fast_tanh(f2hi(hh)));
+            h = f2mul(h, f2fma(t, half2, half2));
+          }
+          if (kDense) {
+            f2_t sc = bs[i], sh = bh[i];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+              sc = f2fma(ws[i][k], pk[k], sc);
+              sh = f2fma(wh[i][k], pk[k], sh);
+            }
+            h = f2fma(h, sc, sh);
+          }
+          w[u][i] = pack_bf16x2(f2lo(h), f2hi(h));
+        }
+        const long long out_row = out_img + (a.out_padded ? prow[u] : p);
+        __nv_bfloat16* dst = a.y + out_row * a.ldy + c0;
+        if (VEC == 8)
+          *reinterpret_cast<uint4*>(dst) = make_uint4(w[u][0], w[u][1], w[u][NP - 2], w[u][NP - 1]);
+        else
+          *reinterpret_cast<uint2*>(dst) = make_uint2(w[u][0], w[u][1]);
+      }
+    }
   }
 
   // zero border of a padded output image (first pixel-chunk block of each image)
@@ -209,6 +250,151 @@ gn_apply_kernel(const GNApplyArgs a) {
         *reinterpret_cast<uint4*>(a.y + row * a.ldy + c0) = make_uint4(0u, 0u, 0u, 0u);
       else
         *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dense (Plucker-modulated) apply with an in-smem prefetch ring.  The 4x2x6 modulation weights pin ~60
+// registers per thread, so only ~15 warps fit per SM and register-held loads cannot cover the HBM latency
+// (ncu: 4.4 warps per issue slot stalled on the long scoreboard, 1.8 TB/s).  Here every thread keeps
+// kRing 8-byte cp.async row loads of its own channel vector in flight in shared memory (~60 KB per SM),
+// and only ever reads what it copied itself (cp.async.wait_group, no block barrier).
+// ------------------------------------------------------------------------------------------------
+constexpr int kGnRing = 16;
+
+__global__ void __launch_bounds__(512)
+gn_apply_dense_kernel(const GNApplyArgs a) {
+  extern __shared__ float gstat[];  // [groups][2] mean, rstd, then the ring [kGnRing][blockDim.x] x 8 B
+  const int n = blockIdx.y;
+  const int cpg = a.C / a.groups;
+  const int HW = a.H * a.W;
+  const int Wp = a.W + 2;
+  const long long rpi_pad = (long long)(a.H + 2) * Wp;
+  for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
+    const float* sp = a.sums + ((long long)n * a.C + g * cpg) * 2;
+    float s = 0.f, q = 0.f;
+    for (int c = 0; c < cpg; ++c) {
+      s += sp[2 * c];
+      q += sp[2 * c + 1];
+    }
+    const float cnt = (float)cpg * (float)HW;
+    const float mean = s / cnt;
+    const float var = fmaxf(q / cnt - mean * mean, 0.0f);
+    gstat[2 * g] = mean;
+    gstat[2 * g + 1] = rsqrtf(var + a.eps);
+  }
+  __syncthreads();
+  const uint32_t ring = smem_u32(gstat) + ((2 * a.groups * 4 + 15) & ~15) + threadIdx.x * 8;
+  const uint32_t ring_pitch = blockDim.x * 8;
+
+  const int CG = a.cslice / 4;
+  const int cg = threadIdx.x % CG;
+  const int pl = threadIdx.x / CG;
+  const int PPB = blockDim.x / CG;
+  const int c0 = blockIdx.z * a.cslice + cg * 4;
+  f2_t sa[2], sb[2], ws[2][6], wh[2][6], bs[2], bh[2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float ta[2], tb[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * i + e;
+      const int g = c / cpg;
+      const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
+      const float ga = a.gamma[c], be = a.beta[c];
+      ta[e] = rstd * ga;
+      tb[e] = fmaf(-mean, rstd * ga, be);
+    }
+    sa[i] = f2(ta[0], ta[1]);
+    sb[i] = f2(tb[0], tb[1]);
+    const int c = c0 + 2 * i;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      ws[i][k] = f2(a.dense_w[(long long)c * 6 + k], a.dense_w[(long long)(c + 1) * 6 + k]);
+      wh[i][k] = f2(a.dense_w[(long long)(a.C + c) * 6 + k], a.dense_w[(long long)(a.C + c + 1) * 6 + k]);
+    }
+    bs[i] = f2(1.0f + a.dense_b[c], 1.0f + a.dense_b[c + 1]);  // fold the "1 +" of h*(1+scale)
+    bh[i] = f2(a.dense_b[a.C + c], a.dense_b[a.C + c + 1]);
+  }
+
+  const int p_begin = blockIdx.x * a.pix_per_block;
+  const int p_end = min(HW, p_begin + a.pix_per_block);
+  const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
+  const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
+  const f2_t half2 = f2(0.5f, 0.5f);
+  auto padded_row = [&](int p) {
+    const int yy = (int)__umulhi((unsigned)p, a.w_magic);
+    return p + 2 * yy + Wp + 1;  // (yy + 1) * Wp + xx + 1
+  };
+  auto prefetch = [&](int p, int slot) {
+    if (p < p_end) {
+      const long long in_row = in_img + (a.in_padded ? padded_row(p) : p);
+      const __nv_bfloat16* src = a.x + in_row * a.ldx + c0;
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring + slot * ring_pitch), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const int p0 = p_begin + pl;
+#pragma unroll
+  for (int d = 0; d < kGnRing; ++d) prefetch(p0 + d * PPB, d);
+  int slot = 0;
+  // the 6 Plucker values of a pixel are fetched two pixels ahead (L1/L2 hits, but ~300 cycles when exposed)
+  auto load_dense = [&](int p, float2 (&d)[3]) {
+    if (p < p_end) {
+      const float2* dp = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p) * 6);
+      d[0] = __ldg(dp); d[1] = __ldg(dp + 1); d[2] = __ldg(dp + 2);
+    }
+  };
+  float2 dA[3], dB[3];
+  load_dense(p0, dA);
+  load_dense(p0 + PPB, dB);
+  for (int p = p0; p < p_end; p += PPB) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kGnRing - 1) : "memory");
+    uint32_t w0, w1;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(ring + slot * ring_pitch) : "memory");
+    prefetch(p + kGnRing * PPB, slot);  // refill the slot just consumed
+    slot = slot + 1 == kGnRing ? 0 : slot + 1;
+    const float2 d0 = dA[0], d1 = dA[1], d2 = dA[2];
+    dA[0] = dB[0]; dA[1] = dB[1]; dA[2] = dB[2];
+    load_dense(p + 2 * PPB, dB);
+    f2_t pk[6];
+    pk[0] = f2(d0.x, d0.x); pk[1] = f2(d0.y, d0.y); pk[2] = f2(d1.x, d1.x);
+    pk[3] = f2(d1.y, d1.y); pk[4] = f2(d2.x, d2.x); pk[5] = f2(d2.y, d2.y);
+    uint32_t wv[2] = {w0, w1};
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      f2_t h = f2fma(f2(bf16_lo(wv[i]), bf16_hi(wv[i])), sa[i], sb[i]);
+      if (a.silu) {  // x * sigmoid(x), sigmoid(x) = 0.5 * tanh(0.5 x) + 0.5
+        const f2_t hh = f2mul(h, half2);
+        const f2_t t = f2(fast_tanh(f2lo(hh)), fast_tanh(f2hi(hh)));
+        h = f2mul(h, f2fma(t, half2, half2));
+      }
+      f2_t sc = bs[i], sh = bh[i];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        sc = f2fma(ws[i][k], pk[k], sc);
+        sh = f2fma(wh[i][k], pk[k], sh);
+      }
+      h = f2fma(h, sc, sh);
+      wv[i] = pack_bf16x2(f2lo(h), f2hi(h));
+    }
+    const long long out_row = out_img + (a.out_padded ? padded_row(p) : p);
+    *reinterpret_cast<uint2*>(a.y + out_row * a.ldy + c0) = make_uint2(wv[0], wv[1]);
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+  // zero border of a padded output image (first pixel-chunk block of each image)
+  if (a.out_padded && blockIdx.x == 0) {
+    const int Hp = a.H + 2;
+    const int nborder = 2 * Wp + 2 * a.H;
+    for (int i = pl; i < nborder; i += PPB) {
+      int yy, xx;
+      if (i < Wp) { yy = 0; xx = i; }
+      else if (i < 2 * Wp) { yy = Hp - 1; xx = i - Wp; }
+      else { const int k = i - 2 * Wp; yy = 1 + (k >> 1); xx = (k & 1) ? Wp - 1 : 0; }
+      const long long row = out_img + (long long)yy * Wp + xx;
+      *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
     }
   }
 }
@@ -323,7 +509,6 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   SEVA_CHECK(p->C > 0 && p->groups > 0 && (p->C % p->groups) == 0 && (p->C % 4) == 0,
              "seva_groupnorm_apply: bad C=%d groups=%d", p->C, p->groups);
   SEVA_CHECK((p->ldx % 4) == 0 && (p->ldy % 4) == 0, "seva_groupnorm_apply: ldx/ldy must be multiples of 4");
-  SEVA_CHECK(p->C / 4 <= 640, "seva_groupnorm_apply: C too large (%d)", p->C);
   SEVA_CHECK(!p->dense || (p->dense_w && p->dense_b), "seva_groupnorm_apply: dense needs dense_w/dense_b");
   GNApplyArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(p->x);
@@ -344,28 +529,45 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   a.dense = p->dense;
   a.dense_w = p->dense_w;
   a.dense_b = p->dense_b;
-  // dense modulation keeps 4x2x7 weights per thread in registers -> 4-channel groups (8-byte accesses);
-  // the plain path uses 8-channel groups (16-byte accesses) when the strides allow it
+  // dense modulation keeps 4x2x6 weights per thread in registers -> 4-channel vectors (8-byte accesses);
+  // the plain path uses 8-channel vectors (16-byte accesses) when the strides allow it
   const bool vec8 = !p->dense && (p->C % 8) == 0 && (p->ldx % 8) == 0 && (p->ldy % 8) == 0 &&
                     (((uintptr_t)p->x | (uintptr_t)p->y) & 15) == 0;
-  const int CG = p->C / (vec8 ? 8 : 4);
+  const int vec = vec8 ? 8 : 4;
+  // channel slices of at most 512 vectors per block (blockIdx.z)
+  int nslice = 1;
+  while ((p->C / vec + nslice - 1) / nslice > 512 || (p->C % (nslice * vec)) != 0) {
+    ++nslice;
+    SEVA_CHECK(nslice <= 64, "seva_groupnorm_apply: cannot slice C=%d", p->C);
+  }
+  a.cslice = p->C / nslice;
+  const int CG = a.cslice / vec;
   int ppb = 512 / CG;
   if (ppb < 1) ppb = 1;
   const int threads = CG * ppb;
   const int HW = p->H * p->Wd;
-  // ~3 blocks per SM over the batch; each block walks >= 4 pixel rounds so its register set-up is amortised
-  long long pix = ((long long)HW * p->Nimg + (long long)sm_count() * 3 - 1) / ((long long)sm_count() * 3);
-  if (pix < 4 * ppb) pix = 4 * ppb;
+  const int unroll = p->dense ? 8 : 4;
+  a.w_magic = (unsigned)((0x100000000ull + (unsigned)p->Wd - 1) / (unsigned)p->Wd);
+  SEVA_CHECK((unsigned long long)HW * p->Wd < 0x100000000ull, "seva_groupnorm_apply: image too large");
+  // ~2 resident blocks per SM over the batch; each block walks >= 2 unrolled rounds
+  long long pix = ((long long)HW * p->Nimg * nslice + (long long)sm_count() * 2 - 1) / ((long long)sm_count() * 2);
+  if (pix < 2ll * ppb * unroll) pix = 2ll * ppb * unroll;
   if (pix > HW) pix = HW;
   a.pix_per_block = (int)pix;
-  dim3 grid((HW + a.pix_per_block - 1) / a.pix_per_block, p->Nimg);
+  dim3 grid((HW + a.pix_per_block - 1) / a.pix_per_block, p->Nimg, nslice);
   const size_t smem = sizeof(float) * 2 * p->groups;
-  if (p->dense)
-    gn_apply_kernel<true, 4><<<grid, threads, smem, stream>>>(a);
-  else if (vec8)
-    gn_apply_kernel<false, 8><<<grid, threads, smem, stream>>>(a);
+  if (p->dense) {
+    const size_t smem_d = ((smem + 15) & ~(size_t)15) + (size_t)kGnRing * threads * 8;
+    static bool attr_set = false;
+    if (!attr_set) {
+      SEVA_CUDA(cudaFuncSetAttribute(gn_apply_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      attr_set = true;
+    }
+    gn_apply_dense_kernel<<<grid, threads, smem_d, stream>>>(a);
+  } else if (vec8)
+    gn_apply_kernel<false, 8, 4><<<grid, threads, smem, stream>>>(a);
   else
-    gn_apply_kernel<false, 4><<<grid, threads, smem, stream>>>(a);
+    gn_apply_kernel<false, 4, 4><<<grid, threads, smem, stream>>>(a);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
