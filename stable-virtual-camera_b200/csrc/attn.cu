@@ -9,10 +9,19 @@
 //   warp 0       TMA producer: Q0, Q1 once; K_j / V_j through an 8-entry ring of 16 KB tiles
 //   warp 1       MMA issuer:   S_i = Q_i K_j^T  (SS, 128x128x64)  and  O_i += P_i V_j (TS, 128x64x128)
 //   warp 2       TMEM allocator
-//   warps 4-7    softmax for Q tile 0: one thread per row, online softmax in registers (exp2, scale
-//   warps 8-11   softmax for Q tile 1  folded into one FFMA), lazy O rescale, P written back to TMEM
-// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384); P_i (bf16, 64 columns) aliases S_i.
-// The tensor pipe executes in issue order, so "PV_i(j) then S_i(j+1)" needs no extra barrier.
+//   warps 4-7    softmax for Q tile 0: one thread per row; the whole 128-column S row is pulled into
+//   warps 8-11   softmax for Q tile 1  registers in one pass (224 registers per thread via setmaxnreg), so
+//                the S columns are handed back to the tensor pipe BEFORE the exponentials start and
+//                S_i(j+1) is computed underneath softmax_i(j).  P goes to its own TMEM columns.
+// TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512)  (P is bf16).
+// Per (tile i, key block j) hand-offs, all mbarriers with phase j & 1:
+//   bar_s[i]      MMA -> softmax   S_i(j) complete                      (tcgen05.commit)
+//   bar_sfree[i]  softmax -> MMA   S_i(j) is in registers               (one arrival per warp)
+//   bar_p[i]      softmax -> MMA   P_i(j) is in TMEM                    (one arrival per warp)
+//   bar_pv[i]     MMA -> softmax   O_i += P_i(j) V_j complete: P_i and O_i may be touched again
+// The MUFU unit (16 ex2/clk/SM) is the ceiling of this kernel at head dim 64 (128x128 exponentials
+// against 512 tensor-pipe clocks per tile pair), so a fixed fraction of the exponentials is evaluated on
+// the FMA pipe instead (Cody-Waite split + cubic, relative error 7.5e-5, far below the bf16 rounding of P).
 #include "common.cuh"
 #include "../../include/seva_b200.h"
 
@@ -24,6 +33,11 @@ constexpr int kRing = 8;                 // K/V ring entries (16 KB each)
 constexpr int kTileBytes = 128 * 64 * 2; // 16 KB
 constexpr int kAttnCtrl = 1024;
 constexpr int kAttnSmem = kAttnCtrl + 1024 + (2 + kRing) * kTileBytes;
+constexpr int kRegsLow = 56;             // TMA / MMA / allocator warpgroup
+constexpr int kRegsHigh = 224;           // softmax warpgroups
+#ifndef SEVA_ATTN_EMU
+#define SEVA_ATTN_EMU 4                  // pairs out of every 16 whose exp2 runs on the FMA pipe
+#endif
 
 struct AttnArgs {
   int B, Hh, Lq, Lk;
@@ -36,6 +50,9 @@ struct AttnArgs {
 __device__ __forceinline__ unsigned long long pack2f(float lo, float hi) {
   return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
 }
+__device__ __forceinline__ unsigned long long pack2u(uint32_t lo, uint32_t hi) {
+  return (unsigned long long)lo | ((unsigned long long)hi << 32);
+}
 __device__ __forceinline__ unsigned long long ffma2(unsigned long long a, unsigned long long b,
                                                     unsigned long long c) {
   unsigned long long d;
@@ -47,103 +64,120 @@ __device__ __forceinline__ unsigned long long fadd2(unsigned long long a, unsign
   asm("add.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+__device__ __forceinline__ float lo2f(unsigned long long v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi2f(unsigned long long v) { return __uint_as_float((uint32_t)(v >> 32)); }
 
-template <bool kTail>
-__device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], int col0, int kv_valid, float mx) {
-  float m0 = mx, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-#pragma unroll
-  for (int t = 0; t < 32; t += 4) {
-    if (!kTail || col0 + t + 0 < kv_valid) m0 = fmaxf(m0, __uint_as_float(v[t + 0]));
-    if (!kTail || col0 + t + 1 < kv_valid) m1 = fmaxf(m1, __uint_as_float(v[t + 1]));
-    if (!kTail || col0 + t + 2 < kv_valid) m2 = fmaxf(m2, __uint_as_float(v[t + 2]));
-    if (!kTail || col0 + t + 3 < kv_valid) m3 = fmaxf(m3, __uint_as_float(v[t + 3]));
-  }
-  return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+template <int kRegs>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
+}
+template <int kRegs>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
 }
 
-// P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; returns the partial row sum
-template <bool kTail>
-__device__ __forceinline__ void chunk_exp(const uint32_t (&v)[32], int col0, int kv_valid,
-                                          unsigned long long sl2_2, unsigned long long negm_2,
-                                          uint32_t (&pk)[16], unsigned long long& sum2) {
+// exp2 of two values on the FMA pipe: x = n + f with n = round(x), f in [-0.5, 0.5];
+// 2^f by a cubic (minimax in relative error, 7.5e-5), 2^n by adding n to the exponent field.
+__device__ __forceinline__ unsigned long long exp2_poly2(unsigned long long x2) {
+  constexpr float kMagic = 12582912.0f;  // 1.5 * 2^23: the low mantissa bits of x + kMagic hold round(x)
+  const float x0 = fmaxf(lo2f(x2), -125.0f), x1 = fmaxf(hi2f(x2), -125.0f);
+  const unsigned long long xc = pack2f(x0, x1);
+  const unsigned long long t = fadd2(xc, pack2f(kMagic, kMagic));
+  const unsigned long long n = fadd2(t, pack2f(-kMagic, -kMagic));
+  const unsigned long long f = ffma2(n, pack2f(-1.0f, -1.0f), xc);
+  constexpr float kC0 = 0.9999280571937561f, kC1 = 0.6932609677314758f, kC2 = 0.2426111251115799f,
+                  kC3 = 0.0551716648042202f;
+  unsigned long long p = ffma2(pack2f(kC3, kC3), f, pack2f(kC2, kC2));
+  p = ffma2(p, f, pack2f(kC1, kC1));
+  p = ffma2(p, f, pack2f(kC0, kC0));
+  const uint32_t r0 = (uint32_t)p + ((uint32_t)t << 23);
+  const uint32_t r1 = (uint32_t)(p >> 32) + ((uint32_t)(t >> 32) << 23);
+  return pack2u(r0, r1);
+}
+
+__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+
+// P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; accumulates the row sum
+__device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long sl2_2,
+                                          unsigned long long negm_2, uint32_t (&pk)[16],
+                                          unsigned long long& sum2) {
 #pragma unroll
   for (int t = 0; t < 16; ++t) {
-    const unsigned long long x2 =
-        ffma2((unsigned long long)v[2 * t] | ((unsigned long long)v[2 * t + 1] << 32), sl2_2, negm_2);
-    float p0 = fast_exp2(__uint_as_float((uint32_t)x2));
-    float p1 = fast_exp2(__uint_as_float((uint32_t)(x2 >> 32)));
-    if (kTail) {
-      if (col0 + 2 * t >= kv_valid) p0 = 0.0f;
-      if (col0 + 2 * t + 1 >= kv_valid) p1 = 0.0f;
+    const unsigned long long x2 = ffma2(pack2u(v[2 * t], v[2 * t + 1]), sl2_2, negm_2);
+    unsigned long long p2;
+    if (((t + 1) * SEVA_ATTN_EMU) / 16 != (t * SEVA_ATTN_EMU) / 16) {  // evenly spread, compile-time
+      p2 = exp2_poly2(x2);
+    } else {
+      p2 = pack2f(fast_exp2(lo2f(x2)), fast_exp2(hi2f(x2)));
     }
-    sum2 = fadd2(sum2, pack2f(p0, p1));
-    pk[t] = pack_bf16x2(p0, p1);
+    sum2 = fadd2(sum2, p2);
+    pk[t] = pack_bf16x2(lo2f(p2), hi2f(p2));
   }
 }
 
-// Online-softmax update for one 128x128 S tile of this thread's row: row max (pass 1), lazy O rescale,
-// P = exp2(.) written over the first 64 columns of S (pass 2).  TMEM loads are issued one chunk ahead.
+// One key block of the online softmax for this thread's row.
 template <bool kTail>
-__device__ __forceinline__ void softmax_tile(uint32_t tS, uint32_t tO, float sl2, int kv_valid, int j,
+__device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree,
+                                             uint32_t bar_pv, float sl2, int kv_valid, int j, int lane,
                                              float& m_run, float& l_run) {
-  uint32_t va[32], vb[32];
-  // ---- pass 1: row max
-  tmem_ld32(tS, va);
-  tmem_ld32(tS + 32, vb);
+  uint32_t s[128];
+  tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+  tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+  tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&s[64]));
+  tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&s[96]));
   tmem_wait_ld();
-  float mx = chunk_max<kTail>(va, 0, kv_valid, -INFINITY);
-  tmem_ld32(tS + 64, va);
-  mx = chunk_max<kTail>(vb, 32, kv_valid, mx);
-  tmem_ld32(tS + 96, vb);
-  tmem_wait_ld();
-  mx = chunk_max<kTail>(va, 64, kv_valid, mx);
-  // start pass 2's first load before finishing pass 1's last reduction
-  tmem_ld32(tS, va);
-  mx = chunk_max<kTail>(vb, 96, kv_valid, mx);
-
+  // the row is in registers: give the S columns back so that S(j+1) runs underneath this softmax
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar_sfree);
+  if (kTail) {
+#pragma unroll
+    for (int c = 0; c < 128; ++c)
+      if (c >= kv_valid) s[c] = 0xff800000u;  // -inf: exp2 gives 0
+  }
+  float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+  for (int c = 0; c < 128; c += 8) {
+    m0 = max3(m0, __uint_as_float(s[c + 0]), __uint_as_float(s[c + 1]));
+    m1 = max3(m1, __uint_as_float(s[c + 2]), __uint_as_float(s[c + 3]));
+    m2 = max3(m2, __uint_as_float(s[c + 4]), __uint_as_float(s[c + 5]));
+    m3 = max3(m3, __uint_as_float(s[c + 6]), __uint_as_float(s[c + 7]));
+  }
+  const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
   const float m_new = fmaxf(m_run, mx * sl2);
   if (j == 0) {
     m_run = m_new;
   } else {
     const bool need = m_new > m_run + 8.0f;
+    // O_i and P_i belong to the tensor pipe until PV_i(j-1) has completed
+    mbar_wait(bar_pv, (j - 1) & 1);
+    tc_fence_after();
     if (__any_sync(0xffffffffu, need)) {
-      tmem_wait_ld();
       const float alpha = fast_exp2(m_run - m_new);
       l_run *= alpha;
       m_run = m_new;
 #pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld32(tO + c * 32, vb);
+      for (int c = 0; c < 4; ++c) {
+        uint32_t vo[16];
+        tmem_ld16(tO + c * 16, vo);
         tmem_wait_ld();
 #pragma unroll
-        for (int t = 0; t < 32; ++t) vb[t] = __float_as_uint(__uint_as_float(vb[t]) * alpha);
-        tmem_st32(tO + c * 32, vb);
+        for (int t = 0; t < 16; ++t) vo[t] = __float_as_uint(__uint_as_float(vo[t]) * alpha);
+        tmem_st16(tO + c * 16, vo);
       }
     }
   }
-  // ---- pass 2: P = exp2(s*scale_log2 - m_run) as packed bf16 over S columns [0, 64)
   const unsigned long long sl2_2 = pack2f(sl2, sl2);
   const unsigned long long negm_2 = pack2f(-m_run, -m_run);
   unsigned long long sum2 = 0ull;
-  uint32_t pk[16];
-  tmem_wait_ld();                       // chunk 0 in va
-  tmem_ld32(tS + 32, vb);               // prefetch chunk 1
-  chunk_exp<kTail>(va, 0, kv_valid, sl2_2, negm_2, pk, sum2);
-  tmem_wait_ld();                       // chunk 1 in vb (chunk 0 fully consumed)
-  tmem_st16(tS, pk);                    // P cols [0,16) overlap only S chunk 0
-  tmem_ld32(tS + 64, va);               // prefetch chunk 2
-  chunk_exp<kTail>(vb, 32, kv_valid, sl2_2, negm_2, pk, sum2);
-  tmem_wait_ld();
-  tmem_st16(tS + 16, pk);               // cols [16,32): S chunk 0, consumed
-  tmem_ld32(tS + 96, vb);               // prefetch chunk 3
-  chunk_exp<kTail>(va, 64, kv_valid, sl2_2, negm_2, pk, sum2);
-  tmem_wait_ld();
-  tmem_st16(tS + 32, pk);               // cols [32,48): S chunk 1, consumed
-  chunk_exp<kTail>(vb, 96, kv_valid, sl2_2, negm_2, pk, sum2);
-  tmem_st16(tS + 48, pk);               // cols [48,64): S chunk 1, consumed
-  l_run += __uint_as_float((uint32_t)sum2) + __uint_as_float((uint32_t)(sum2 >> 32));
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint32_t pk[16];
+    chunk_exp(&s[32 * c], sl2_2, negm_2, pk, sum2);
+    tmem_st16(tP + 16 * c, pk);
+  }
+  l_run += lo2f(sum2) + hi2f(sum2);
 }
-
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -154,9 +188,10 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const uint32_t bar_full = smem_base + 8;           // kRing
   const uint32_t bar_empty = bar_full + 8 * kRing;   // kRing
   const uint32_t bar_s = bar_empty + 8 * kRing;      // 2
-  const uint32_t bar_p = bar_s + 16;                 // 2
-  const uint32_t bar_o = bar_p + 16;                 // 2
-  const uint32_t tmem_slot = bar_o + 16;
+  const uint32_t bar_sfree = bar_s + 16;             // 2
+  const uint32_t bar_p = bar_sfree + 16;             // 2
+  const uint32_t bar_pv = bar_p + 16;                // 2
+  const uint32_t tmem_slot = bar_pv + 16;
   const uint32_t q_smem = smem_base + kAttnCtrl;           // 2 tiles
   const uint32_t ring_smem = q_smem + 2 * kTileBytes;      // kRing tiles
 
@@ -178,8 +213,9 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s + 8 * i, 1);
-      mbar_init(bar_p + 8 * i, 128);
-      mbar_init(bar_o + 8 * i, 1);
+      mbar_init(bar_sfree + 8 * i, 4);
+      mbar_init(bar_p + 8 * i, 4);
+      mbar_init(bar_pv + 8 * i, 1);
     }
     fence_barrier_init();
   }
@@ -190,104 +226,125 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp == 0) {
-    // ------------------------------------ TMA producer -----------------------------------------
-    // all lanes run the loop (addresses stay warp-uniform / in uniform registers); one elected lane issues
-    if (elect_one()) {
-      mbar_expect_tx(bar_q, 2 * kTileBytes);
-      tma_load_3d(q_smem, &tmQ, bar_q, head * 64, q0, b);
-      tma_load_3d(q_smem + kTileBytes, &tmQ, bar_q, head * 64, q0 + 128, b);
-    }
-    __syncwarp();
-    uint32_t s = 0, ph = 0;
-    for (int e = 0; e < 2 * nkv; ++e) {
-      const int j = e >> 1;
-      mbar_wait(bar_empty + 8 * s, ph ^ 1);
+  if (warp < 4) {
+    setmaxnreg_dec<kRegsLow>();
+    if (warp == 0) {
+      // ---------------------------------- TMA producer -----------------------------------------
+      // all lanes run the loop (addresses stay warp-uniform / in uniform registers); one elected lane issues
       if (elect_one()) {
-        mbar_expect_tx(bar_full + 8 * s, kTileBytes);
-        tma_load_3d(ring_smem + s * kTileBytes, (e & 1) ? &tmV : &tmK, bar_full + 8 * s, head * 64, j * 128, b);
+        mbar_expect_tx(bar_q, 2 * kTileBytes);
+        tma_load_3d(q_smem, &tmQ, bar_q, head * 64, q0, b);
+        tma_load_3d(q_smem + kTileBytes, &tmQ, bar_q, head * 64, q0 + 128, b);
       }
       __syncwarp();
-      if (++s == kRing) { s = 0; ph ^= 1; }
-    }
-  } else if (warp == 1) {
-    // ------------------------------------ MMA issuer --------------------------------------------
-    // whole warp runs the (uniform) schedule; one elected lane issues each group of MMAs + commits
-    const uint32_t idesc_qk = make_idesc_bf16(128, 128, 0, 0);
-    const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major (d contiguous)
-    const uint64_t qdesc0 = make_sdesc_sw128(q_smem, 16, 1024);
-    const uint64_t qdesc1 = make_sdesc_sw128(q_smem + kTileBytes, 16, 1024);
-    auto ring_wait = [&](int e) { mbar_wait(bar_full + 8 * (e % kRing), (e / kRing) & 1); };
-    auto ring_addr = [&](int e) { return ring_smem + (e % kRing) * kTileBytes; };
-    auto issue_s = [&](int i, int e_k) {
-      const uint64_t kdesc = make_sdesc_sw128(ring_addr(e_k), 16, 1024);
-      const uint64_t qd = i ? qdesc1 : qdesc0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
-    };
-    auto issue_pv = [&](int i, int e_v, int j) {
-      const uint32_t vaddr = ring_addr(e_v);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart; P columns advance by 8
-        const uint64_t vdesc = make_sdesc_sw128(vaddr + k * 2048, 8192, 1024);
-        umma_ts(tmem_base + 256 + i * 64, tmem_base + i * 128 + k * 8, vdesc, idesc_pv,
-                (j | k) != 0 ? 1u : 0u);
+      // ring order = the order in which the MMA warp consumes and frees the tiles: K0, then per key block j
+      // [K(j+1)], V(j)
+      uint32_t s = 0, ph = 0;
+      auto load = [&](const CUtensorMap* tm, int j) {
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(bar_full + 8 * s, kTileBytes);
+          tma_load_3d(ring_smem + s * kTileBytes, tm, bar_full + 8 * s, head * 64, j * 128, b);
+        }
+        __syncwarp();
+        if (++s == kRing) { s = 0; ph ^= 1; }
+      };
+      load(&tmK, 0);
+      for (int j = 0; j < nkv; ++j) {
+        if (j + 1 < nkv) load(&tmK, j + 1);
+        load(&tmV, j);
       }
-    };
+    }
+    if (warp == 1) {
+      // ---------------------------------- MMA issuer --------------------------------------------
+      // whole warp runs the (uniform) schedule; one elected lane issues each group of MMAs + commits
+      const uint32_t idesc_qk = make_idesc_bf16(128, 128, 0, 0);
+      const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major (d contiguous)
+      const uint64_t qdesc0 = make_sdesc_sw128(q_smem, 16, 1024);
+      const uint64_t qdesc1 = make_sdesc_sw128(q_smem + kTileBytes, 16, 1024);
+      uint32_t rs = 0, rph = 0;  // ring cursor
+      auto ring_next = [&]() { if (++rs == kRing) { rs = 0; rph ^= 1; } };
+      auto issue_s = [&](int i, uint32_t kaddr) {
+        const uint64_t kdesc = make_sdesc_sw128(kaddr, 16, 1024);
+        const uint64_t qd = i ? qdesc1 : qdesc0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
+      };
+      auto issue_pv = [&](int i, uint32_t vaddr, int j) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart; P columns advance by 8
+          const uint64_t vdesc = make_sdesc_sw128(vaddr + k * 2048, 8192, 1024);
+          umma_ts(tmem_base + 256 + i * 64, tmem_base + 384 + i * 64 + k * 8, vdesc, idesc_pv,
+                  (j | k) != 0 ? 1u : 0u);
+        }
+      };
 
-    mbar_wait(bar_q, 0);
-    ring_wait(0);
-    tc_fence_after();
-    if (elect_one()) {
-      issue_s(0, 0);
-      tc_commit(bar_s);
-      issue_s(1, 0);
-      tc_commit(bar_s + 8);
-      tc_commit(bar_empty + 0);
-    }
-    __syncwarp();
-    for (int j = 0; j < nkv; ++j) {
-      const int e_v = 2 * j + 1, e_kn = 2 * j + 2;
-      const bool has_next = j + 1 < nkv;
-      ring_wait(e_v);
-      if (has_next) ring_wait(e_kn);
-      mbar_wait(bar_p, j & 1);
+      mbar_wait(bar_q, 0);
+      mbar_wait(bar_full + 8 * rs, rph);
       tc_fence_after();
       if (elect_one()) {
-        issue_pv(0, e_v, j);
-        if (has_next) {
-          issue_s(0, e_kn);
-          tc_commit(bar_s);
-        } else {
-          tc_commit(bar_o);
-        }
+        issue_s(0, ring_smem + rs * kTileBytes);
+        tc_commit(bar_s);
+        issue_s(1, ring_smem + rs * kTileBytes);
+        tc_commit(bar_s + 8);
+        tc_commit(bar_empty + 8 * rs);
       }
       __syncwarp();
-      mbar_wait(bar_p + 8, j & 1);
-      tc_fence_after();
-      if (elect_one()) {
-        issue_pv(1, e_v, j);
-        tc_commit(bar_empty + 8 * (e_v % kRing));
-        if (has_next) {
-          issue_s(1, e_kn);
-          tc_commit(bar_s + 8);
-          tc_commit(bar_empty + 8 * (e_kn % kRing));
-        } else {
-          tc_commit(bar_o + 8);
+      ring_next();
+      for (int j = 0; j < nkv; ++j) {
+        if (j + 1 < nkv) {
+          // S_i(j+1) as soon as softmax_i has pulled S_i(j) into registers
+          mbar_wait(bar_full + 8 * rs, rph);
+          const uint32_t kaddr = ring_smem + rs * kTileBytes;
+          mbar_wait(bar_sfree, j & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            issue_s(0, kaddr);
+            tc_commit(bar_s);
+          }
+          __syncwarp();
+          mbar_wait(bar_sfree + 8, j & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            issue_s(1, kaddr);
+            tc_commit(bar_s + 8);
+            tc_commit(bar_empty + 8 * rs);
+          }
+          __syncwarp();
+          ring_next();
         }
+        mbar_wait(bar_full + 8 * rs, rph);
+        const uint32_t vaddr = ring_smem + rs * kTileBytes;
+        mbar_wait(bar_p, j & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          issue_pv(0, vaddr, j);
+          tc_commit(bar_pv);
+        }
+        __syncwarp();
+        mbar_wait(bar_p + 8, j & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          issue_pv(1, vaddr, j);
+          tc_commit(bar_pv + 8);
+          tc_commit(bar_empty + 8 * rs);
+        }
+        __syncwarp();
+        ring_next();
       }
-      __syncwarp();
     }
-  } else if (warp >= 4) {
+  } else {
     // ------------------------------------ softmax + epilogue ------------------------------------
+    setmaxnreg_inc<kRegsHigh>();
     const int i = (warp - 4) >> 2;     // Q tile handled by this warpgroup
     const int quarter = warp & 3;      // TMEM lane quarter
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
     const uint32_t tS = tmem_base + lane_sel + i * 128;
     const uint32_t tO = tmem_base + lane_sel + 256 + i * 64;
+    const uint32_t tP = tmem_base + lane_sel + 384 + i * 64;
     const float sl2 = a.scale_log2;
     float m_run = -INFINITY;  // running max of s*scale*log2(e) (possibly stale by < 8)
     float l_run = 0.0f;
@@ -297,16 +354,17 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       tc_fence_after();
       const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
       if (kv_valid >= 128)
-        softmax_tile<false>(tS, tO, sl2, 128, j, m_run, l_run);
+        softmax_step<false>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, m_run, l_run);
       else
-        softmax_tile<true>(tS, tO, sl2, kv_valid, j, m_run, l_run);
+        softmax_step<true>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, m_run, l_run);
       tmem_wait_st();
       tc_fence_before();
-      mbar_arrive(bar_p + 8 * i);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p + 8 * i);
     }
 
     // epilogue: O_i / l -> bf16 -> global
-    mbar_wait(bar_o + 8 * i, 0);
+    mbar_wait(bar_pv + 8 * i, (nkv - 1) & 1);
     tc_fence_after();
     const int qrow = q0 + i * 128 + row;
     const float inv_l = 1.0f / l_run;
