@@ -23,6 +23,7 @@
 // against 512 tensor-pipe clocks per tile pair), so a fixed fraction of the exponentials is evaluated on
 // the FMA pipe instead (Cody-Waite split + cubic, relative error 7.5e-5, far below the bf16 rounding of P).
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/seva_b200.h"
 
 namespace seva {
@@ -35,9 +36,7 @@ constexpr int kAttnCtrl = 1024;
 constexpr int kAttnSmem = kAttnCtrl + 1024 + (2 + kRing) * kTileBytes;
 constexpr int kRegsLow = 56;             // TMA / MMA / allocator warpgroup
 constexpr int kRegsHigh = 224;           // softmax warpgroups
-#ifndef SEVA_ATTN_EMU
-#define SEVA_ATTN_EMU 4                  // pairs out of every 16 whose exp2 runs on the FMA pipe
-#endif
+constexpr int kEmuDefault = 4;           // pairs out of every 16 whose exp2 runs on the FMA pipe
 
 struct AttnArgs {
   int B, Hh, Lq, Lk;
@@ -98,6 +97,7 @@ __device__ __forceinline__ unsigned long long exp2_poly2(unsigned long long x2) 
 __device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 
 // P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; accumulates the row sum
+template <int kEmu>
 __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long sl2_2,
                                           unsigned long long negm_2, uint32_t (&pk)[16],
                                           unsigned long long& sum2) {
@@ -105,7 +105,7 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
   for (int t = 0; t < 16; ++t) {
     const unsigned long long x2 = ffma2(pack2u(v[2 * t], v[2 * t + 1]), sl2_2, negm_2);
     unsigned long long p2;
-    if (((t + 1) * SEVA_ATTN_EMU) / 16 != (t * SEVA_ATTN_EMU) / 16) {  // evenly spread, compile-time
+    if (((t + 1) * kEmu) / 16 != (t * kEmu) / 16) {  // evenly spread, compile-time
       p2 = exp2_poly2(x2);
     } else {
       p2 = pack2f(fast_exp2(lo2f(x2)), fast_exp2(hi2f(x2)));
@@ -116,7 +116,7 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
 }
 
 // One key block of the online softmax for this thread's row.
-template <bool kTail>
+template <bool kTail, int kEmu>
 __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree,
                                              uint32_t bar_pv, float sl2, int kv_valid, int j, int lane,
                                              float& m_run, float& l_run) {
@@ -173,12 +173,13 @@ __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t 
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     uint32_t pk[16];
-    chunk_exp(&s[32 * c], sl2_2, negm_2, pk, sum2);
+    chunk_exp<kEmu>(&s[32 * c], sl2_2, negm_2, pk, sum2);
     tmem_st16(tP + 16 * c, pk);
   }
   l_run += lo2f(sum2) + hi2f(sum2);
 }
 
+template <int kEmu>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -348,15 +349,14 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const float sl2 = a.scale_log2;
     float m_run = -INFINITY;  // running max of s*scale*log2(e) (possibly stale by < 8)
     float l_run = 0.0f;
-
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(bar_s + 8 * i, j & 1);
       tc_fence_after();
       const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
       if (kv_valid >= 128)
-        softmax_step<false>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, m_run, l_run);
+        softmax_step<false, kEmu>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, m_run, l_run);
       else
-        softmax_step<true>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, m_run, l_run);
+        softmax_step<true, kEmu>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, m_run, l_run);
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
@@ -443,14 +443,25 @@ extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* 
   a.ldo = ldo;
   a.bso = bso;
   a.scale_log2 = scale * 1.4426950408889634f;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   kAttnSmem));
-    attr_set = true;
+  // developer knob: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 selects the fraction (n/16) of exponentials on the FMA pipe
+  static int emu = -1;
+  if (emu < 0) {
+    const char* e = getenv("SEVA_ATTN_EMU");
+    emu = e ? atoi(e) : kEmuDefault;
+    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
   }
   dim3 grid((Lq + 255) / 256, Hh, B);
-  attn_kernel<<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);
+  switch (emu) {
+    case 0: attn_kernel<0><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+    case 2: attn_kernel<2><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+    case 6: attn_kernel<6><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+    case 8: attn_kernel<8><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+    default: attn_kernel<4><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+  }
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
