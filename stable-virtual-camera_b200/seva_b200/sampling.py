@@ -327,11 +327,14 @@ class EulerEDMSampler(object):
             x = x + eps * append_dims(sigma_hat**2 - sigma**2, x.ndim) ** 0.5
 
         denoised = denoiser(*self.guider.prepare_inputs(x, sigma_hat, cond, uc))
+        guide = self.guider
+        if hasattr(guide, "gather"):  # dist.CFGSplit: this rank denoised one half; restore [uncond; cond]
+            denoised, guide = guide.gather(denoised), guide.guider
         frame_scale = self._fused_scale(x, sigma_hat, scale, guider_kwargs) if fused else None
         if frame_scale is not None and denoised.dtype == torch.float32 and denoised.shape[0] == 2 * x.shape[0] \
                 and (x[0].numel() % 4) == 0:
             return ops.cfg_euler_step(x, denoised, frame_scale, sigma_hat.contiguous(), next_sigma.contiguous())
-        denoised = self.guider(denoised, sigma_hat, scale, **guider_kwargs)
+        denoised = guide(denoised, sigma_hat, scale, **guider_kwargs)
         d = to_d(x, sigma_hat, denoised)
         dt = append_dims(next_sigma - sigma_hat, x.ndim)
         return x + dt * d
