@@ -37,11 +37,14 @@ def _lin(sd, k, x):
     return F.linear(x, sd[k + ".weight"], sd.get(k + ".bias"))
 
 
-def _attention(sd, k, x, context, heads):
-    """transformer.py:59-74"""
+def _attention(sd, k, x, context, heads, kv_gather=None):
+    """transformer.py:59-74.  ``kv_gather`` (frame sequence-parallel check only): maps this rank's K / V
+    [batch, local keys, C] to the keys of all frames."""
     q = _lin(sd, k + ".to_q", x)
     ctx = x if context is None else context
     kk, v = _lin(sd, k + ".to_k", ctx), _lin(sd, k + ".to_v", ctx)
+    if kv_gather is not None:
+        kk, v = kv_gather(kk), kv_gather(v)
     sp = lambda t: t.reshape(t.shape[0], t.shape[1], heads, -1).transpose(1, 2)
     o = F.scaled_dot_product_attention(sp(q), sp(kk), sp(v))
     o = o.transpose(1, 2).reshape(x.shape[0], x.shape[1], -1)
@@ -75,13 +78,19 @@ def resblock(sd, k, x, emb, dense):
     return x + h
 
 
-def multiview_transformer(sd, k, x, context, T, heads, unflatten):
-    """transformer.py:215-247 with depth 1"""
+def multiview_transformer(sd, k, x, context, T, heads, unflatten, sp=None):
+    """transformer.py:215-247 with depth 1.  With ``sp`` (frame sequence-parallel restatement) ``x`` and
+    ``context`` hold this rank's T frames of every batch element, ``sp.ctx0`` is ``context[::T_total]`` of the
+    full batch and ``sp.gather(t, per_frame)`` concatenates dim 1 of ``t`` over the ranks (per_frame = keys per
+    frame): only the 3D and the time-mix self-attention see other ranks' frames."""
     n, c, h, w = x.shape
     x_in = x
-    time_ctx = context[::T].repeat_interleave(h * w, dim=0)  # "b ... -> (b n) ..." (:222-226)
+    ctx0 = context[::T] if sp is None else sp.ctx0
+    g3 = None if sp is None else (lambda t: sp.gather(t, h * w))
+    gt = None if sp is None else (lambda t: sp.gather(t, 1))
+    time_ctx = ctx0.repeat_interleave(h * w, dim=0)  # "b ... -> (b n) ..." (:222-226)
     if unflatten:
-        context = context[::T]
+        context = ctx0
     x = F.group_norm(x, 32, sd[k + ".norm.weight"], sd[k + ".norm.bias"], 1e-6)
     x = x.permute(0, 2, 3, 1).reshape(n, h * w, c)
     x = _lin(sd, k + ".proj_in", x)
@@ -89,7 +98,7 @@ def multiview_transformer(sd, k, x, context, T, heads, unflatten):
     if unflatten:
         x = x.reshape(n // T, T * h * w, c)
     # TransformerBlock.forward (:106-110)
-    x = _attention(sd, tb + ".attn1", _ln(sd, tb + ".norm1", x), None, heads) + x
+    x = _attention(sd, tb + ".attn1", _ln(sd, tb + ".norm1", x), None, heads, g3 if unflatten else None) + x
     x = _attention(sd, tb + ".attn2", _ln(sd, tb + ".norm2", x), context, heads) + x
     x = _ff(sd, tb + ".ff", _ln(sd, tb + ".norm3", x)) + x
     if unflatten:
@@ -98,7 +107,7 @@ def multiview_transformer(sd, k, x, context, T, heads, unflatten):
     s = h * w
     y = x.reshape(n // T, T, s, c).transpose(1, 2).reshape(-1, T, c)
     y = _ff(sd, tm + ".ff_in", _ln(sd, tm + ".norm_in", y)) + y
-    y = _attention(sd, tm + ".attn1", _ln(sd, tm + ".norm1", y), None, heads) + y
+    y = _attention(sd, tm + ".attn1", _ln(sd, tm + ".norm1", y), None, heads, gt) + y
     y = _attention(sd, tm + ".attn2", _ln(sd, tm + ".norm2", y), time_ctx, heads) + y
     y = _ff(sd, tm + ".ff", _ln(sd, tm + ".norm3", y))
     y = y.reshape(n // T, s, T, c).transpose(1, 2).reshape(n, s, c)
@@ -139,8 +148,8 @@ def block_layout(params):
     return inp, mid, out
 
 
-def seva_forward(sd, params, x, t, y, dense_y, num_frames=None):
-    """Seva.forward, model.py:176-216 (fp32)."""
+def seva_forward(sd, params, x, t, y, dense_y, num_frames=None, sp=None):
+    """Seva.forward, model.py:176-216 (fp32).  ``sp``: see multiview_transformer (num_frames = local frames)."""
     T = num_frames or params.num_frames
     emb = timestep_embedding(t, params.model_channels)
     emb = _lin(sd, "time_embed.2", F.silu(_lin(sd, "time_embed.0", emb)))
@@ -154,7 +163,7 @@ def seva_forward(sd, params, x, t, y, dense_y, num_frames=None):
             elif layer[0] == "res":
                 h = resblock(sd, k, h, emb, dense_y)
             elif layer[0] == "mvt":
-                h = multiview_transformer(sd, k, h, y, T, layer[1], layer[2] in params.unflatten_names)
+                h = multiview_transformer(sd, k, h, y, T, layer[1], layer[2] in params.unflatten_names, sp)
             elif layer[0] == "down":
                 h = F.conv2d(h, sd[k + ".op.weight"], sd[k + ".op.bias"], stride=2, padding=1)
             elif layer[0] == "up":

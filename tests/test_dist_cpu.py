@@ -92,6 +92,38 @@ def _run_sampler(guider, x0, c, uc, c2w, K, mask, steps=4):
                    uc={k: v.clone() for k, v in uc.items()}, verbose=False, c2w=c2w, K=K, input_frame_mask=mask)
 
 
+class _OracleFrameGather:
+    """sp hook of oracle.seva_forward over a real process group: K/V of the other ranks' frames via allgather_rows."""
+
+    def __init__(self, ctx0, counts, group=None):
+        self.ctx0, self.counts, self.group = ctx0, counts, group
+
+    def gather(self, t, per_frame):
+        cnt = [c * per_frame for c in self.counts]
+        src = t.transpose(0, 1).contiguous()
+        out = torch.empty((sum(cnt),) + tuple(src.shape[1:]), dtype=t.dtype)
+        D.allgather_rows(out, cnt, src, self.group)
+        return out.transpose(0, 1)
+
+
+def _sp_problem(T=5, B=2, h=16, w=16):
+    from oracle import seva_oracle as O
+    from oracle import synth
+    from seva_b200.model import Seva, SevaParams
+
+    P = SevaParams(model_channels=64, num_frames=T)
+    with torch.device("meta"):
+        m = Seva(P)
+    sd = synth.fill_state_dict({k: tuple(v.shape) for k, v in m.state_dict().items()}, seed=0)
+    g = torch.Generator().manual_seed(5)
+    n = B * T
+    x = torch.randn(n, P.in_channels, h, w, generator=g)
+    t = torch.full((n,), 499, dtype=torch.int64)
+    y = torch.randn(n, 1, P.context_dim, generator=g)  # a different token per frame: context[::T] must be frame 0's
+    dense = torch.randn(n, 6, h, w, generator=g)
+    return O, P, sd, x, t, y, dense
+
+
 def _worker(rank, world, port, ret):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -116,6 +148,16 @@ def _worker(rank, world, port, ret):
         x0, c, uc, c2w, K, mask = _sampling_inputs()
         guider = D.CFGSplit(S.MultiviewCFG(1.2), groups["cfg"], half=topo.half)
         out["cfg_split"] = _run_sampler(guider, x0, c, uc, c2w, K, mask)
+        # frame sequence-parallel restatement: each rank owns 3 / 2 of the 5 frames of both batch elements
+        O, P, sd, x, t, y, dense = _sp_problem()
+        T, B = 5, 2
+        parts = D.partition_frames(T, world)
+        t0, t1 = parts[rank]
+        loc = lambda a: a.view(B, T, *a.shape[1:])[:, t0:t1].reshape(B * (t1 - t0), *a.shape[1:])
+        sp = _OracleFrameGather(y[::T], [b - a for a, b in parts])
+        with torch.inference_mode():
+            o_loc = O.seva_forward(sd, P, loc(x), loc(t), loc(y), loc(dense), num_frames=t1 - t0, sp=sp)
+        out["sp_local"] = o_loc.clone()
         ret[rank] = out
     finally:
         dist.destroy_process_group()
@@ -155,3 +197,17 @@ def test_cfg_split_matches_single_process(two_ranks):
     ref = _run_sampler(S.MultiviewCFG(1.2), x0, c, uc, c2w, K, mask)
     for r in range(2):
         assert torch.equal(two_ranks[r]["cfg_split"], ref)
+
+
+def test_frame_sequence_parallel_restatement(two_ranks):
+    """Frames 0-2 on rank 0, 3-4 on rank 1, K/V exchanged only at the 3D and time-mix self-attention: equals the
+    one-process forward (fp32, reduction order inside SDPA differs -> 1e-4)."""
+    O, P, sd, x, t, y, dense = _sp_problem()
+    with torch.inference_mode():
+        ref = O.seva_forward(sd, P, x, t, y, dense, num_frames=5)
+    ref = ref.view(2, 5, *ref.shape[1:])
+    parts = D.partition_frames(5, 2)
+    for r, (t0, t1) in enumerate(parts):
+        got = two_ranks[r]["sp_local"].view(2, t1 - t0, *ref.shape[2:])
+        err = ((got - ref[:, t0:t1]).norm() / ref[:, t0:t1].norm()).item()
+        assert err < 1e-4, (r, err)
