@@ -84,6 +84,12 @@ int seva_attn_fwd(const void* q, const void* k, const void* v, void* o, int32_t 
  * for every (b, s, h) softmax over t' of the T frames.  out [B*T*S, C] (row stride ldo). */
 int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t T, int32_t S, int32_t Hh,
                       int64_t ldqkv, int64_t ldo, float scale, void* stream);
+/* Same op with the queries and the keys/values in separate buffers and Tq <= Tk frames (frame sequence-parallel
+ * ranks hold Tq of the Tk frames): q rows (b*Tq + t)*S + s (stride ldq), k / v rows (b*Tk + t)*S + s
+ * (stride ldkv), out rows like q (stride ldo). */
+int seva_timemix_attn_kv(const void* q, const void* k, const void* v, void* out, int32_t B, int32_t Tq,
+                         int32_t Tk, int32_t S, int32_t Hh, int64_t ldq, int64_t ldkv, int64_t ldo,
+                         float scale, void* stream);
 
 /* ---- normalisation ---------------------------------------------------------------------------- */
 /* Per-(image, channel) sum and sum of squares over rpi rows: sums[n, c, 0:2] (fp32, zeroed inside). */

@@ -15,8 +15,9 @@ constexpr int kTmWarps = 4;
 
 template <int TMAX>
 __global__ void __launch_bounds__(kTmWarps * 32)
-timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int B, int T,
-                    int S, int Hh, long long ldqkv, long long ldo, float scale_log2) {
+timemix_attn_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __restrict__ kp,
+                    const __nv_bfloat16* __restrict__ vp, __nv_bfloat16* __restrict__ out, int B, int Tq, int T,
+                    int S, int Hh, long long ldq, long long ldkv, long long ldo, float scale_log2) {
   // per warp: K [T][32 words], V [T][32 words], Q [32][33 words]
   extern __shared__ uint32_t sm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -27,7 +28,6 @@ timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
   const long long bs = item / Hh;
   const int s = (int)(bs % S);
   const int b = (int)(bs / S);
-  const int C = Hh * 64;
   uint32_t* ks = sm + warp * (2 * TMAX * 32 + 32 * 33);
   uint32_t* vs = ks + TMAX * 32;
   uint32_t* qs = vs + TMAX * 32;
@@ -37,28 +37,27 @@ timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
   for (int t0 = 0; t0 < T; t0 += 4) {
     const int t = t0 + sub;
     if (t < T) {
-      const long long row = ((long long)b * T + t) * S + s;
-      const __nv_bfloat16* base = qkv + row * ldqkv + h * 64 + part * 8;
-      const uint4 kq = __ldg(reinterpret_cast<const uint4*>(base + C));
-      const uint4 vq = __ldg(reinterpret_cast<const uint4*>(base + 2 * C));
+      const long long off = (((long long)b * T + t) * S + s) * ldkv + h * 64 + part * 8;
+      const uint4 kq = __ldg(reinterpret_cast<const uint4*>(kp + off));
+      const uint4 vq = __ldg(reinterpret_cast<const uint4*>(vp + off));
       *reinterpret_cast<uint4*>(ks + t * 32 + part * 4) = kq;
       *reinterpret_cast<uint4*>(vs + t * 32 + part * 4) = vq;
     }
   }
-  for (int qb = 0; qb < T; qb += 32) {
+  for (int qb = 0; qb < Tq; qb += 32) {
     __syncwarp();
     for (int t0 = 0; t0 < 32; t0 += 4) {
       const int t = qb + t0 + sub;
-      if (t < T) {
-        const long long row = ((long long)b * T + t) * S + s;
-        const uint4 qq = __ldg(reinterpret_cast<const uint4*>(qkv + row * ldqkv + h * 64 + part * 8));
+      if (t < Tq) {
+        const long long row = ((long long)b * Tq + t) * S + s;
+        const uint4 qq = __ldg(reinterpret_cast<const uint4*>(qp + row * ldq + h * 64 + part * 8));
         uint32_t* d = qs + (t0 + sub) * 33 + part * 4;
         d[0] = qq.x; d[1] = qq.y; d[2] = qq.z; d[3] = qq.w;
       }
     }
     __syncwarp();
     const int tq = qb + lane;
-    const bool active = tq < T;
+    const bool active = tq < Tq;
     float q[64];
 #pragma unroll
     for (int w = 0; w < 32; ++w) {
@@ -107,7 +106,7 @@ timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
       }
       if (active) {
         const float inv_l = 1.0f / l_run;
-        const long long row = ((long long)b * T + tq) * S + s;
+        const long long row = ((long long)b * Tq + tq) * S + s;
         uint4* o4 = reinterpret_cast<uint4*>(out + row * ldo + h * 64);
 #pragma unroll
         for (int w4 = 0; w4 < 8; ++w4) {
@@ -173,7 +172,7 @@ timemix_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __rest
       }
     }
     if (active) {
-      const long long row = ((long long)b * T + tq) * S + s;
+      const long long row = ((long long)b * Tq + tq) * S + s;
       uint4* o4 = reinterpret_cast<uint4*>(out + row * ldo + h * 64);
 #pragma unroll
       for (int w4 = 0; w4 < 8; ++w4) {
@@ -221,14 +220,14 @@ __device__ __forceinline__ uint32_t tm_off(int row, int chunk) {
 }
 
 __global__ void __launch_bounds__(kTmmWarps * 32, 4)
-timemix_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out, int B, int T,
-                   int S, int Hh, long long ldqkv, long long ldo, float scale_log2, long long total,
+timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __restrict__ kp,
+                   const __nv_bfloat16* __restrict__ vp, __nv_bfloat16* __restrict__ out, int B, int Tq, int T,
+                   int S, int Hh, long long ldq, long long ldkv, long long ldo, float scale_log2, long long total,
                    long long nwarps_total) {
   extern __shared__ __align__(128) uint8_t tm_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t qS = smem_u32(tm_smem) + warp * kTmmBytes;
   const uint32_t kS = qS + 4096, vS = qS + 8192;
-  const int C = Hh * 64;
   const int sub = lane >> 3, part = lane & 7;  // staging: 8 lanes x 16 B per row, 4 rows per instruction
   const int g = lane >> 2, q4 = lane & 3;      // fragment coordinates
   // rows >= T stay zero for the whole kernel (V rows meet P = 0 there: they must be finite)
@@ -245,25 +244,26 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
     __syncwarp();  // the previous item's output staging has been read
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
-      if (half * 16 < T) {
+      if (half * 16 < T || half * 16 < Tq) {
         uint4 lq[4], lk[4], lv[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
           const int t = half * 16 + 4 * r + sub;
+          if (t < Tq)
+            lq[r] = __ldg(reinterpret_cast<const uint4*>(qp + (((long long)b * Tq + t) * S + s) * ldq + h * 64 + part * 8));
           if (t < T) {
-            const long long row = ((long long)b * T + t) * S + s;
-            const __nv_bfloat16* base = qkv + row * ldqkv + h * 64 + part * 8;
-            lq[r] = __ldg(reinterpret_cast<const uint4*>(base));
-            lk[r] = __ldg(reinterpret_cast<const uint4*>(base + C));
-            lv[r] = __ldg(reinterpret_cast<const uint4*>(base + 2 * C));
+            const long long off = (((long long)b * T + t) * S + s) * ldkv + h * 64 + part * 8;
+            lk[r] = __ldg(reinterpret_cast<const uint4*>(kp + off));
+            lv[r] = __ldg(reinterpret_cast<const uint4*>(vp + off));
           }
         }
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
           const int t = half * 16 + 4 * r + sub;
-          if (t < T) {
-            const uint32_t o = tm_off(t, part);
+          const uint32_t o = tm_off(t, part);
+          if (t < Tq)
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(qS + o), "r"(lq[r].x), "r"(lq[r].y), "r"(lq[r].z), "r"(lq[r].w) : "memory");
+          if (t < T) {
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(kS + o), "r"(lk[r].x), "r"(lk[r].y), "r"(lk[r].z), "r"(lk[r].w) : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(vS + o), "r"(lv[r].x), "r"(lv[r].y), "r"(lv[r].z), "r"(lv[r].w) : "memory");
           }
@@ -371,10 +371,10 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
       const int t = 4 * r + sub;
-      if (t < T) {
+      if (t < Tq) {
         uint4 u;
         asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(qS + tm_off(t, part)) : "memory");
-        const long long row = ((long long)b * T + t) * S + s;
+        const long long row = ((long long)b * Tq + t) * S + s;
         *reinterpret_cast<uint4*>(out + row * ldo + h * 64 + part * 8) = u;
       }
     }
@@ -383,27 +383,34 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
   }
 }
 
-int launch_timemix_mma(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int T, int S, int Hh,
-                       long long ldqkv, long long ldo, float scale_log2, cudaStream_t stream) {
+struct TmArgs {
+  const __nv_bfloat16 *q, *k, *v;
+  __nv_bfloat16* out;
+  int B, Tq, Tk, S, Hh;
+  long long ldq, ldkv, ldo;
+  float scale_log2;
+};
+
+int launch_timemix_mma(const TmArgs& a, cudaStream_t stream) {
   const size_t smem = (size_t)kTmmWarps * kTmmBytes;
   static bool attr_set = false;
   if (!attr_set) {
     SEVA_CUDA(cudaFuncSetAttribute(timemix_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  const long long total = (long long)B * S * Hh;
+  const long long total = (long long)a.B * a.S * a.Hh;
   long long grid = 4ll * sm_count();  // 16 warps per SM, each striding over items
   const long long need = (total + kTmmWarps - 1) / kTmmWarps;
   if (grid > need) grid = need;
-  timemix_mma_kernel<<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(qkv, out, B, T, S, Hh, ldqkv, ldo,
-                                                                       scale_log2, total, grid * kTmmWarps);
+  timemix_mma_kernel<<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(a.q, a.k, a.v, a.out, a.B, a.Tq, a.Tk, a.S,
+                                                                       a.Hh, a.ldq, a.ldkv, a.ldo, a.scale_log2,
+                                                                       total, grid * kTmmWarps);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
 
 template <int TMAX>
-int launch_timemix(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int T, int S, int Hh,
-                   long long ldqkv, long long ldo, float scale_log2, cudaStream_t stream) {
+int launch_timemix(const TmArgs& a, cudaStream_t stream) {
   const size_t smem = sizeof(uint32_t) * kTmWarps * (2 * TMAX * 32 + 32 * 33);
   static bool attr_set = false;
   if (!attr_set) {
@@ -411,33 +418,54 @@ int launch_timemix(const __nv_bfloat16* qkv, __nv_bfloat16* out, int B, int T, i
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  const long long total = (long long)B * S * Hh;
+  const long long total = (long long)a.B * a.S * a.Hh;
   const long long grid = (total + kTmWarps - 1) / kTmWarps;
   SEVA_CHECK(grid < (1ll << 31), "seva_timemix_attn: grid too large");
-  timemix_attn_kernel<TMAX><<<(unsigned)grid, kTmWarps * 32, smem, stream>>>(qkv, out, B, T, S, Hh, ldqkv,
-                                                                             ldo, scale_log2);
+  timemix_attn_kernel<TMAX><<<(unsigned)grid, kTmWarps * 32, smem, stream>>>(
+      a.q, a.k, a.v, a.out, a.B, a.Tq, a.Tk, a.S, a.Hh, a.ldq, a.ldkv, a.ldo, a.scale_log2);
   SEVA_CUDA(cudaGetLastError());
   return 0;
+}
+
+int timemix_dispatch(const TmArgs& a, cudaStream_t stream) {
+  if (a.Tk <= 32) return launch_timemix_mma(a, stream);
+  if (a.Tk <= 64) return launch_timemix<64>(a, stream);
+  return launch_timemix<128>(a, stream);
 }
 
 }  // namespace
 }  // namespace seva
 
-extern "C" int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t T, int32_t S, int32_t Hh,
-                                 int64_t ldqkv, int64_t ldo, float scale, void* stream_v) {
+extern "C" int seva_timemix_attn_kv(const void* q, const void* k, const void* v, void* out, int32_t B, int32_t Tq,
+                                    int32_t Tk, int32_t S, int32_t Hh, int64_t ldq, int64_t ldkv, int64_t ldo,
+                                    float scale, void* stream_v) {
   using namespace seva;
   if (check_device()) return 3;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
-  SEVA_CHECK(qkv && out, "seva_timemix_attn: null pointer");
-  SEVA_CHECK(B > 0 && T > 0 && S > 0 && Hh > 0, "seva_timemix_attn: bad sizes");
-  SEVA_CHECK(T <= 128, "seva_timemix_attn: T=%d > 128 frames is not supported", T);
-  SEVA_CHECK((ldqkv % 8) == 0 && (ldo % 8) == 0, "seva_timemix_attn: strides must be multiples of 8");
-  SEVA_CHECK(((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0,
+  SEVA_CHECK(q && k && v && out, "seva_timemix_attn: null pointer");
+  SEVA_CHECK(B > 0 && Tq > 0 && Tk > 0 && S > 0 && Hh > 0, "seva_timemix_attn: bad sizes");
+  SEVA_CHECK(Tk <= 128, "seva_timemix_attn: T=%d > 128 frames is not supported", Tk);
+  SEVA_CHECK(Tq <= Tk, "seva_timemix_attn: more query frames (%d) than key frames (%d)", Tq, Tk);
+  SEVA_CHECK((ldq % 8) == 0 && (ldkv % 8) == 0 && (ldo % 8) == 0,
+             "seva_timemix_attn: strides must be multiples of 8");
+  SEVA_CHECK(((uintptr_t)q & 15) == 0 && ((uintptr_t)k & 15) == 0 && ((uintptr_t)v & 15) == 0 &&
+                 ((uintptr_t)out & 15) == 0,
              "seva_timemix_attn: pointers must be 16-byte aligned");
-  const __nv_bfloat16* qp = reinterpret_cast<const __nv_bfloat16*>(qkv);
-  __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(out);
-  const float sl2 = scale * 1.4426950408889634f;
-  if (T <= 32) return launch_timemix_mma(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
-  if (T <= 64) return launch_timemix<64>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
-  return launch_timemix<128>(qp, op, B, T, S, Hh, ldqkv, ldo, sl2, stream);
+  TmArgs a;
+  a.q = reinterpret_cast<const __nv_bfloat16*>(q);
+  a.k = reinterpret_cast<const __nv_bfloat16*>(k);
+  a.v = reinterpret_cast<const __nv_bfloat16*>(v);
+  a.out = reinterpret_cast<__nv_bfloat16*>(out);
+  a.B = B; a.Tq = Tq; a.Tk = Tk; a.S = S; a.Hh = Hh;
+  a.ldq = ldq; a.ldkv = ldkv; a.ldo = ldo;
+  a.scale_log2 = scale * 1.4426950408889634f;
+  return timemix_dispatch(a, stream);
+}
+
+extern "C" int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t T, int32_t S, int32_t Hh,
+                                 int64_t ldqkv, int64_t ldo, float scale, void* stream_v) {
+  SEVA_CHECK(qkv != nullptr, "seva_timemix_attn: null pointer");
+  const uint16_t* p = reinterpret_cast<const uint16_t*>(qkv);
+  const int64_t C = (int64_t)Hh * 64;
+  return seva_timemix_attn_kv(p, p + C, p + 2 * C, out, B, T, T, S, Hh, ldqkv, ldqkv, ldo, scale, stream_v);
 }

@@ -51,6 +51,7 @@ _PROTOS = {
     "seva_gemm_pick_bn": [c_int, c_int],
     "seva_attn_fwd": [c_void_p] * 4 + [c_int] * 4 + [c_i64] * 8 + [c_float, c_void_p],
     "seva_timemix_attn": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_i64, c_i64, c_float, c_void_p],
+    "seva_timemix_attn_kv": [c_void_p] * 4 + [c_int] * 5 + [c_i64] * 3 + [c_float, c_void_p],
     "seva_groupnorm_stats": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_void_p],
     "seva_groupnorm_apply": [C.POINTER(SevaGNApply), c_void_p],
     "seva_layernorm": [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],

@@ -98,10 +98,65 @@ def pack_weights(model: Seva) -> dict:
 
 
 # ----------------------------------------------------------------------------------------------------
+# frame sequence-parallel shard: this rank owns frames [t0, t1) of every batch element
+# ----------------------------------------------------------------------------------------------------
+class FrameShard:
+    def __init__(self, group, T_total: int, size: int | None = None, rank: int | None = None):
+        """``size`` / ``rank`` default to the process group's; passing them builds the shard of another rank for the
+        one-process emulation of the frame group (tests/test_model_gpu.py), whose ``gather`` must not be called."""
+        from .dist import partition_frames
+
+        self.group = group
+        if size is None:
+            import torch.distributed as dist
+
+            size, rank = dist.get_world_size(group), dist.get_rank(group)
+        self.size, self.rank = size, rank
+        self.T_total = T_total
+        self.parts = partition_frames(T_total, self.size)
+        self.t0, self.t1 = self.parts[self.rank]
+        self.counts = [b - a for a, b in self.parts]
+        if min(self.counts) < 1:
+            raise SevaB200Error(f"{T_total} frames cannot be split over {self.size} ranks (a rank would own none)")
+
+    @property
+    def T_local(self) -> int:
+        return self.t1 - self.t0
+
+    def local(self, x: torch.Tensor, B: int) -> torch.Tensor:
+        """[B*T_total, ...] -> this rank's [B*T_local, ...] (contiguous copy)."""
+        return x.reshape(B, self.T_total, *x.shape[1:])[:, self.t0:self.t1].reshape(B * self.T_local, *x.shape[1:]) \
+            .contiguous()
+
+    def gather(self, out: torch.Tensor, loc: torch.Tensor, B: int, rows_per_frame: int) -> None:
+        """out [B*T_total*rpf, C] <- every rank's loc [B*T_r*rpf, C], frames in global order per batch element."""
+        from .dist import allgather_rows
+
+        cnt = [c * rows_per_frame for c in self.counts]
+        nl, nf = self.T_local * rows_per_frame, self.T_total * rows_per_frame
+        for b in range(B):
+            allgather_rows(out[b * nf:(b + 1) * nf], cnt, loc[b * nl:(b + 1) * nl], self.group)
+
+
+class _FrameGather:
+    """Plan entry (called like a C-ABI launch): K/V of all frames <- the frame group."""
+    __name__ = "frame_gather_kv"
+
+    def __init__(self, shard: FrameShard, out, loc, B, rows_per_frame):
+        self.a = (shard, out, loc, B, rows_per_frame)
+
+    def __call__(self, stream) -> int:
+        shard, out, loc, B, rpf = self.a
+        shard.gather(out, loc, B, rpf)
+        return 0
+
+
+# ----------------------------------------------------------------------------------------------------
 # plan
 # ----------------------------------------------------------------------------------------------------
 class Engine:
-    def __init__(self, model: Seva, packed: dict, n: int, num_frames: int, h: int, w: int, ctx_len: int):
+    def __init__(self, model: Seva, packed: dict, n: int, num_frames: int, h: int, w: int, ctx_len: int,
+                 shard: FrameShard | None = None):
         p = model.params
         nlev = len(p.channel_mult)
         if h % (1 << (nlev - 1)) or w % (1 << (nlev - 1)):
@@ -109,7 +164,12 @@ class Engine:
         self.lib = _lib.load()
         self.dev = next(model.parameters()).device
         self.P = packed
+        # with a frame shard, n / num_frames are LOCAL (this rank's frames); Tk = frames the cross-frame ops see
         self.N, self.T, self.B = n, num_frames, n // num_frames
+        self.shard = shard
+        self.Tk = num_frames if shard is None else shard.T_total
+        if shard is not None and shard.T_local != num_frames:
+            raise SevaB200Error("frame shard / engine frame count mismatch")
         self.h, self.w, self.L = h, w, ctx_len
         self.ctx_dim = p.context_dim
         self.unflatten = set(p.unflatten_names)
@@ -153,7 +213,8 @@ class Engine:
         (2*MAC for Linear/conv on unpadded pixels, 4*B*H*Lq*Lk*D for attention, activation bytes for norms)."""
         self.calls.append((fn, args))
         self.meta.append((fn.__name__, tag, float(flops), float(nbytes)))
-        self.n_launch += 1
+        if not isinstance(fn, _FrameGather):  # collectives are NCCL's kernels, not ours
+            self.n_launch += 1
 
     # ---- op emitters (each appends exactly one kernel launch unless noted) ---------------------
     def gemm(self, A, W, out, *, bias=None, M=None, ntaps=1, tap_wp=0, rowbias=None, rowbias_rpi=0, residual=None,
@@ -412,14 +473,25 @@ class Engine:
         a = self.buf(f"tk_ln_{l}", rc, C_)
         self.ln(x0, w["s_n1"], a)
         qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
-        self.gemm(a, w["s_attn1"]["wqkv"], qkv)
         o = self.buf(f"tk_o_{l}", rc, C_)
         bat, Lseq = (B, T * S) if is3d else (self.N, S)
-        ld = qkv.stride(0)
-        base = qkv.data_ptr()
-        self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
-                 ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
-                 flops=4.0 * bat * heads * Lseq * Lseq * 64, tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
+        sh = self.shard
+        if is3d and sh is not None:
+            # frame sequence-parallel 3D attention: local queries against the keys / values of all Tk frames
+            q, kvl, kvf = self._split_qkv(a, w["s_attn1"]["wqkv"], l, C_, S)
+            Lk = self.Tk * S
+            self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
+                     heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
+                     Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
+                     tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
+        else:
+            self.gemm(a, w["s_attn1"]["wqkv"], qkv)
+            ld = qkv.stride(0)
+            base = qkv.data_ptr()
+            self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
+                     ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
+                     flops=4.0 * bat * heads * Lseq * Lseq * 64,
+                     tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
         x1 = self.buf(f"tk_x1_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
@@ -436,10 +508,17 @@ class Engine:
         y1 = self.buf(f"tk_y1_{l}", rc, C_)
         self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin")
         self.ln(y1, w["t_n1"], a)
-        self.gemm(a, w["t_attn1"]["wqkv"], qkv)
-        self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
-                 o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
-                 tag=f"timemix BS{B * S} H{heads}")
+        if sh is not None:
+            q, kvl, kvf = self._split_qkv(a, w["t_attn1"]["wqkv"], l, C_, S)
+            self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
+                     o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
+                     flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
+                     tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
+        else:
+            self.gemm(a, w["t_attn1"]["wqkv"], qkv)
+            self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
+                     o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
+                     tag=f"timemix BS{B * S} H{heads}")
         y2 = self.buf(f"tk_y2_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
@@ -452,6 +531,17 @@ class Engine:
         self._ff(y2, w["t_n3"], w["t_ff"], x2, x3, l, C_, "t")
         # proj_out + input residual, written back to the zero-bordered layout (transformer.py:244-247)
         self.gemm(x3, w["wout"], out, bias=w["bout"], residual=x, out_map=1, H=H, Wd=Wd)
+
+    def _split_qkv(self, a, wqkv, l, C_, S):
+        """Frame-sharded self-attention input: q for the local frames, [k | v] gathered over the frame group."""
+        rc = a.shape[0]
+        q = self.buf(f"tk_q_{l}", rc, C_)
+        kvl = self.buf(f"tk_kvl_{l}", rc, 2 * C_)
+        kvf = self.buf(f"tk_kvf_{l}", self.B * self.Tk * S, 2 * C_)
+        self.gemm(a, wqkv[:C_], q)
+        self.gemm(a, wqkv[C_:], kvl)
+        self.add(_FrameGather(self.shard, kvf, kvl, self.B, S), nbytes=2.0 * kvf.numel(), tag=f"kv rows{kvf.shape[0]} C{2 * C_}")
+        return q, kvl, kvf
 
     def _cross_general(self, wa, nrm, xin, xout, l, C_, heads, bat, Lseq, ctx):
         """attn2 with Lk > 1 context tokens: LN -> q, k/v from context -> flash attention -> to_out + residual."""
@@ -475,11 +565,13 @@ class Engine:
         self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin)
 
     # ---- execution ------------------------------------------------------------------------------
-    def bind(self, t: torch.Tensor, ctx: torch.Tensor, dense: torch.Tensor) -> None:
-        """Copy the per-call conditioning into the plan's static input buffers (device-to-device)."""
+    def bind(self, t: torch.Tensor, ctx: torch.Tensor, dense: torch.Tensor, ctx0: torch.Tensor | None = None) -> None:
+        """Copy the per-call conditioning into the plan's static input buffers (device-to-device).  ``ctx0`` is
+        ``context[::T]`` (transformer.py:222-229); a frame shard passes the full batch's, since frame 0 may live
+        on another rank."""
         self.t_in.copy_(t.reshape(-1))
         self.ctx_in.copy_(ctx)
-        self.ctx0_in.copy_(ctx[:: self.T])
+        self.ctx0_in.copy_(ctx[:: self.T] if ctx0 is None else ctx0)
         self.dense_in.copy_(dense)
 
     def run(self, timing: list | None = None) -> None:

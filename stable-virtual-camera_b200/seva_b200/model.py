@@ -204,6 +204,7 @@ class Seva(nn.Module):
         self.out = nn.Sequential(GroupNorm32(32, ch), nn.SiLU(), nn.Conv2d(mc, p.out_channels, 3, padding=1))
         self._engines: dict = {}
         self._packed = None
+        self._frame_group = None
         self.register_load_state_dict_post_hook(lambda m, k: m.invalidate())
 
     # ---- engine management --------------------------------------------------------------------
@@ -216,14 +217,24 @@ class Seva(nn.Module):
         self.invalidate()
         return super()._apply(fn, *a, **k)
 
+    def set_frame_group(self, group) -> None:
+        """Frame sequence-parallel execution: the ranks of ``group`` split the ``num_frames`` frames of
+        every forward (``dist.partition_frames``); callers keep passing, and receive, full replicated batches.  Per-frame
+        ops run on the owner of the frame; K/V are exchanged at the 3D and time-mix self-attention.  ``None`` disables."""
+        self._frame_group = group
+        self._engines = {}
+
     def engine(self, n: int, num_frames: int, h: int, w: int, ctx_len: int):
-        from .engine import Engine, pack_weights
+        """Plan for a forward of ``n`` images in sets of ``num_frames`` (global sizes; with a frame group the plan
+        covers this rank's frames and ``engine.shard`` describes the split)."""
+        from .engine import Engine, FrameShard, pack_weights
 
         dev = next(self.parameters()).device
         if dev.type != "cuda":
             raise SevaB200Error("Seva parameters are on %s: seva_b200 runs on sm_100a only (no CPU fallback); "
                                 "move the module with .to('cuda')" % dev)
-        key = (dev.index, n, num_frames, h, w, ctx_len)
+        group = self._frame_group
+        key = (dev.index, n, num_frames, h, w, ctx_len, None if group is None else id(group))
         eng = self._engines.get(key)
         if eng is None:
             ops.check_device()
@@ -234,7 +245,12 @@ class Seva(nn.Module):
                     self._packed = pack_weights(self)
                 if len(self._engines) >= 2:  # plans own GBs of workspace: keep the two most recent shapes
                     self._engines.pop(next(iter(self._engines)))
-                eng = Engine(self, self._packed, n, num_frames, h, w, ctx_len)
+                if group is None:
+                    eng = Engine(self, self._packed, n, num_frames, h, w, ctx_len)
+                else:
+                    shard = FrameShard(group, num_frames)
+                    eng = Engine(self, self._packed, (n // num_frames) * shard.T_local, shard.T_local, h, w, ctx_len,
+                                 shard=shard)
             self._engines[key] = eng
         return eng
 
@@ -248,10 +264,20 @@ class Seva(nn.Module):
         assert cin == self.params.in_channels and n % num_frames == 0
         with torch.autocast("cuda", enabled=False):
             eng = self.engine(n, num_frames, h, w, y.shape[1])
-            ops.pack_nchw(x.float(), eng.net_in)
-            eng.bind(t, y, dense_y)
-            eng.run()
-            out = ops.unpack_nchw(eng.eps, n, self.params.out_channels, h, w)
+            sh = eng.shard
+            if sh is None:
+                ops.pack_nchw(x.float(), eng.net_in)
+                eng.bind(t, y, dense_y)
+                eng.run()
+                out = ops.unpack_nchw(eng.eps, n, self.params.out_channels, h, w)
+            else:  # this rank's frames in, every rank's frames out
+                B = n // num_frames
+                ops.pack_nchw(sh.local(x.float(), B), eng.net_in)
+                eng.bind(sh.local(t, B), sh.local(y.float(), B), sh.local(dense_y.float(), B), ctx0=y[::num_frames])
+                eng.run()
+                loc = ops.unpack_nchw(eng.eps, eng.N, self.params.out_channels, h, w)
+                out = torch.empty((n,) + tuple(loc.shape[1:]), device=loc.device, dtype=loc.dtype)
+                sh.gather(out.view(n, -1), loc.view(eng.N, -1), B, 1)
         return out.to(x.dtype)
 
 

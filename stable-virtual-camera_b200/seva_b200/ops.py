@@ -146,6 +146,22 @@ def timemix_attention(qkv: torch.Tensor, B: int, T: int, S: int, heads: int,
     return out
 
 
+def timemix_attention_kv(q: torch.Tensor, kv: torch.Tensor, B: int, Tq: int, Tk: int, S: int, heads: int,
+                         out: torch.Tensor | None = None) -> torch.Tensor:
+    """Frame-axis attention with Tq local query frames against the Tk frames of ``kv`` = [k | v] (frame
+    sequence-parallel ranks)."""
+    _req(q, torch.bfloat16, "q")
+    _req(kv, torch.bfloat16, "kv")
+    Cc = heads * 64
+    assert q.shape == (B * Tq * S, Cc) and kv.shape == (B * Tk * S, 2 * Cc)
+    if out is None:
+        out = torch.empty((B * Tq * S, Cc), device=q.device, dtype=torch.bfloat16)
+    check(_lib.load().seva_timemix_attn_kv(q.data_ptr(), kv.data_ptr(), kv.data_ptr() + 2 * Cc, out.data_ptr(), B, Tq,
+                                           Tk, S, heads, q.stride(0), kv.stride(0), out.stride(0),
+                                           1.0 / math.sqrt(64.0), _stream()), "seva_timemix_attn_kv")
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # norms
 # ------------------------------------------------------------------------------------------------

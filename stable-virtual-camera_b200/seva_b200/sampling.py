@@ -135,6 +135,9 @@ class DiscreteDenoiser(object):
             idx, _, c_in, c_out = ops.sigma_quantize(sigma.float().reshape(-1), self.sigmas)
             replace = cond.pop("replace", None)  # the reference pops it from the per-step dict (sampling.py:147)
             eng = module.engine(n, num_frames, h, w, cond["crossattn"].shape[1])
+            sh = eng.shard
+            if sh is not None:
+                return self._call_fused_sharded(eng, sh, input, replace, cond, idx, c_in, c_out, num_frames)
             blended = torch.empty((n, 4, h, w), device=input.device, dtype=torch.float32)
             ops.denoise_prepare(input.float().contiguous(), None if replace is None else replace.float().contiguous(),
                                 cond["concat"].float().contiguous(), c_in, eng.net_in, blended, n, n, h, w)
@@ -142,6 +145,24 @@ class DiscreteDenoiser(object):
             eng.run()
             out = torch.empty_like(blended)
             ops.denoise_finish(eng.eps, blended, c_out, out, n, h, w)
+        return out
+
+    def _call_fused_sharded(self, eng, sh, input, replace, cond, idx, c_in, c_out, num_frames):
+        """Frame sequence-parallel form of ``_call_fused``: the same kernels on this rank's frames, then one gather of
+        the denoised frames so that every rank returns the full batch (x stays replicated in the sampler)."""
+        n, _, h, w = input.shape
+        B, nl = n // num_frames, eng.N
+        loc = lambda t: sh.local(t.float(), B)
+        blended = torch.empty((nl, 4, h, w), device=input.device, dtype=torch.float32)
+        ops.denoise_prepare(loc(input), None if replace is None else loc(replace), loc(cond["concat"]), loc(c_in),
+                            eng.net_in, blended, nl, nl, h, w)
+        ctx = cond["crossattn"].float()
+        eng.bind(sh.local(idx, B), sh.local(ctx, B), loc(cond["dense_vector"]), ctx0=ctx[::num_frames])
+        eng.run()
+        out_l = torch.empty_like(blended)
+        ops.denoise_finish(eng.eps, blended, loc(c_out), out_l, nl, h, w)
+        out = torch.empty((n, 4, h, w), device=input.device, dtype=torch.float32)
+        sh.gather(out.view(n, -1), out_l.view(nl, -1), B, 1)
         return out
 
 

@@ -218,6 +218,21 @@ def test_timemix_attention(ops, B, T, S, heads):
     assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
 
 
+@pytest.mark.parametrize("B,Tq,t0,Tk,S,heads", [(2, 11, 0, 21, 81, 5), (2, 10, 11, 21, 40, 2), (1, 8, 56, 64, 30, 2),
+                                                 (2, 3, 18, 21, 50, 1)])
+def test_timemix_attention_kv(ops, B, Tq, t0, Tk, S, heads):
+    """Frame sequence-parallel form: Tq local query frames (global frames t0..t0+Tq) against all Tk frames."""
+    g = torch.Generator(device="cuda").manual_seed(Tq * S)
+    Cc = heads * 64
+    qkv = bf(torch.randn(B, Tk, S, 3 * Cc, device="cuda", generator=g))
+    q = qkv[:, t0:t0 + Tq, :, :Cc].reshape(B * Tq * S, Cc).contiguous()
+    kv = qkv[..., Cc:].reshape(B * Tk * S, 2 * Cc).contiguous()
+    out = ops.timemix_attention_kv(q, kv, B, Tq, Tk, S, heads)
+    full = ops.timemix_attention(qkv.reshape(B * Tk * S, 3 * Cc), B, Tk, S, heads).reshape(B, Tk, S, Cc)
+    ref = full[:, t0:t0 + Tq].reshape(B * Tq * S, Cc)
+    assert rel_l2(out, ref) < 1e-6 if Tk <= 32 else rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+
+
 # ---------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("n_img,H,Wd,Cc,in_pad,out_pad,silu,dense", [
     (2, 9, 9, 64, True, True, True, True),

@@ -1,0 +1,187 @@
+"""Multi-GPU partitioning of the denoising step on B200.
+
+* one GPU: the frame group is emulated as ONE program over all ranks' data -- every rank's plan is built in this
+  process, the plans run in lockstep and the K/V exchange is a device copy -- and must reproduce the unsharded plan;
+* two or more GPUs (``gpurun --gpus 2``): the same through NCCL, one process per GPU, for frame sequence-parallel,
+  CFG split and chunk data-parallel sampling, against the one-GPU result on the same inputs.
+"""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+
+from oracle import seva_oracle as O
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def rel_l2(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-12)).item()
+
+
+def _tiny_model(T, seed=0):
+    from seva_b200.model import Seva, SevaParams, SGMWrapper
+
+    P = SevaParams(model_channels=64, num_frames=T)
+    with torch.device("meta"):
+        m = Seva(P)
+    sd = synth.fill_state_dict({k: tuple(v.shape) for k, v in m.state_dict().items()}, seed=seed)
+    m.load_state_dict(sd, assign=True)
+    return P, SGMWrapper(m.eval()).to("cuda")
+
+
+def _net_inputs(P, B, T, h, w, seed=5):
+    g = torch.Generator().manual_seed(seed)
+    n = B * T
+    x = torch.randn(n, P.in_channels, h, w, generator=g).cuda()
+    t = torch.full((n,), 499, dtype=torch.int64).cuda()
+    y = torch.randn(n, 1, P.context_dim, generator=g).cuda()  # per-frame tokens: context[::T] must be frame 0's
+    dense = torch.randn(n, 6, h, w, generator=g).cuda()
+    return x, t, y, dense
+
+
+@pytest.mark.parametrize("T,B,ranks", [(5, 2, 2), (7, 1, 3), (8, 2, 4)])
+def test_frame_shard_emulated_on_one_gpu(T, B, ranks):
+    from seva_b200 import ops
+    from seva_b200.engine import Engine, FrameShard, _FrameGather, pack_weights
+
+    h = w = 16
+    P, model = _tiny_model(T)
+    seva = model.module
+    x, t, y, dense = _net_inputs(P, B, T, h, w)
+    with torch.inference_mode():
+        ref = seva(x, t, y, dense, num_frames=T)
+        sd = {k: v.detach().float().cpu() for k, v in seva.state_dict().items()}
+        ora = O.seva_forward(sd, P, x.cpu(), t.cpu(), y.cpu(), dense.cpu(), num_frames=T)
+    packed = pack_weights(seva)
+    shards = [FrameShard(None, T, size=ranks, rank=r) for r in range(ranks)]
+    engs = [Engine(seva, packed, B * s.T_local, s.T_local, h, w, 1, shard=s) for s in shards]
+    for e, s in zip(engs, shards):
+        ops.pack_nchw(s.local(x.float(), B), e.net_in)
+        e.bind(s.local(t, B), s.local(y, B), s.local(dense, B), ctx0=y[::T])
+    stream = torch.cuda.current_stream().cuda_stream
+    n_gather = 0
+    for i in range(len(engs[0].calls)):
+        fns = [e.calls[i][0] for e in engs]
+        if isinstance(fns[0], _FrameGather):
+            n_gather += 1
+            assert all(isinstance(f, _FrameGather) for f in fns)
+            rpf = fns[0].a[4]
+            nf = T * rpf
+            for dst in fns:
+                out = dst.a[1]
+                for b in range(B):
+                    for s, src in zip(shards, fns):
+                        nl = s.T_local * rpf
+                        out[b * nf + s.t0 * rpf: b * nf + s.t1 * rpf].copy_(src.a[2][b * nl:(b + 1) * nl])
+        else:
+            for e in engs:
+                fn, args = e.calls[i]
+                assert fn(*args, stream) == 0
+    assert n_gather == 16 + sum(1 for m in seva.modules() if getattr(m, "name", "") in P.unflatten_names)
+    for e, s in zip(engs, shards):
+        loc = ops.unpack_nchw(e.eps, e.N, P.out_channels, h, w).view(B, s.T_local, -1)
+        want = ref.reshape(B, T, -1)[:, s.t0:s.t1]
+        assert rel_l2(loc, want) < 1.5e-2, (s.rank, rel_l2(loc, want))       # two bf16 evaluation orders
+        want = ora.reshape(B, T, -1)[:, s.t0:s.t1]
+        assert rel_l2(loc, want) < 2e-2, (s.rank, rel_l2(loc, want))         # the parity bar: fp32 oracle
+
+
+# ---- real process groups (needs >= 2 GPUs) -----------------------------------------------------------
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _sample(model, inp, T, guider, steps=2):
+    from seva_b200 import sampling as S
+
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device="cuda")
+    sampler = S.EulerEDMSampler(disc, guider, num_steps=steps, s_churn=0.0, s_tmin=0.0, s_tmax=999.0, s_noise=1.0,
+                                verbose=False, device="cuda")
+    dev = lambda d: {k: v.cuda() for k, v in d.items()}
+    eps_iter = iter(inp["eps"])
+    orig = torch.randn_like
+    torch.randn_like = lambda t, *a, **k: next(eps_iter).to(t)
+    try:
+        with torch.inference_mode(), torch.autocast("cuda"):
+            return sampler(lambda i, s, c: denoiser(model, i, s, c, num_frames=T), inp["x0"].clone().cuda(), scale=2.0,
+                           cond=dev(inp["c"]), uc=dev(inp["uc"]), verbose=False, c2w=inp["c2w"].cuda(),
+                           K=inp["K"].cuda(), input_frame_mask=inp["mask"].cuda())
+    finally:
+        torch.randn_like = orig
+
+
+def _nccl_worker(rank, world, port, ret):
+    import torch.distributed as dist
+
+    for p in (ROOT, os.path.join(ROOT, "stable-virtual-camera_b200")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from seva_b200 import dist as D
+    from seva_b200 import geometry as G
+    from seva_b200 import sampling as S
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        T, h, w = 5, 16, 16
+        P, model = _tiny_model(T)
+        plk = lambda s, e, K, hh, ww: G.get_plucker_coordinates(s, e, K, target_size=(hh, ww))
+        inp = synth.make_inputs(T, 1, h, w, plk, seed=1, num_steps=2, ctx_dim=P.context_dim)
+        out = {"single": _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()}
+        # frame sequence-parallel over both ranks (3 + 2 frames)
+        model.module.set_frame_group(dist.group.WORLD)
+        out["frames"] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()
+        model.module.set_frame_group(None)
+        # CFG split: uncond on rank 0, cond on rank 1
+        groups = D.build_groups(D.Topology(world, rank, cfg=2, sp=1))
+        out["cfg"] = _sample(model, inp, T, D.CFGSplit(S.MultiviewCFG(1.2), groups["cfg"])).cpu()
+        # chunk data-parallel: 3 chunks (different seeds) over 2 ranks, gathered everywhere
+        mine = {}
+        for k in D.schedule_chunks(3, world)[rank]:
+            ck = synth.make_inputs(T, 1, h, w, plk, seed=10 + k, num_steps=2, ctx_dim=P.context_dim)
+            mine[k] = _sample(model, ck, T, S.MultiviewCFG(1.2))
+        out["chunks"] = torch.stack(D.gather_chunks(mine, 3)).cpu()
+        if rank == 0:
+            refs = []
+            for k in range(3):
+                ck = synth.make_inputs(T, 1, h, w, plk, seed=10 + k, num_steps=2, ctx_dim=P.context_dim)
+                refs.append(_sample(model, ck, T, S.MultiviewCFG(1.2)).cpu())
+            out["chunks_ref"] = torch.stack(refs)
+        ret[rank] = out
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (gpurun --gpus 2)")
+def test_two_gpu_partitions_match_one_gpu():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, ret)) for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(600)
+            assert p.exitcode == 0, f"worker exit code {p.exitcode}"
+        res = {r: dict(ret[r]) for r in range(2)}
+    single = res[0]["single"]
+    assert torch.equal(res[0]["single"], res[1]["single"])
+    for r in range(2):
+        assert rel_l2(res[r]["frames"], single) < 2e-2, rel_l2(res[r]["frames"], single)
+        assert rel_l2(res[r]["cfg"], single) < 5e-3, rel_l2(res[r]["cfg"], single)
+    assert torch.equal(res[0]["frames"], res[1]["frames"]) and torch.equal(res[0]["cfg"], res[1]["cfg"])
+    assert torch.equal(res[0]["chunks"], res[1]["chunks"])
+    assert torch.equal(res[0]["chunks"], res[0]["chunks_ref"])  # same kernels, same inputs: bit-identical
