@@ -131,10 +131,28 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     T, h, w = args.T, args.size, args.size
     model, _ = build_model(dev)
-    host = make_host_inputs(T, h, w, seed=1 + rank)
+    # --parallel chunks (default): every rank samples its own chunk (weak scaling, no data-path collective)
+    # --parallel cfg:    ONE chunk; uncond / cond halves on rank pairs, remaining factor world/2 splits the frames
+    # --parallel frames: ONE chunk; all ranks split the frames (K/V exchanged at 3D / time-mix attention)
+    guider = S.MultiviewCFG(1.2)
+    chunks_world, par_desc = world, f"dp{world} (one independent T-frame chunk per GPU)" if world > 1 else "single GPU"
+    if world > 1 and args.parallel != "chunks":
+        from seva_b200 import dist as D
+
+        cfg = 2 if args.parallel == "cfg" else 1
+        topo = D.Topology(world, rank, cfg=cfg, sp=world // cfg)
+        groups = D.build_groups(topo)
+        if groups["frames"] is not None:
+            model.module.set_frame_group(groups["frames"])
+        if cfg == 2:
+            guider = D.CFGSplit(guider, groups["cfg"], half=topo.half)
+        chunks_world = 1
+        par_desc = f"one chunk over {world} GPUs: cfg{cfg} x frames{world // cfg}"
+        torch.manual_seed(1234)  # replicated sampler state: identical noise on every rank
+    host = make_host_inputs(T, h, w, seed=1 + (rank if chunks_world > 1 else 0))
     disc = S.DDPMDiscretization()
     denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device=dev)
-    sampler = S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), num_steps=50, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
+    sampler = S.EulerEDMSampler(disc, guider, num_steps=50, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
                                 s_noise=1.0, verbose=False, device=dev)
     sigmas = disc(50, device=dev)
     den_fn = lambda i, s, c: denoiser(model, i, s, c, num_frames=T)
@@ -246,24 +264,25 @@ def run_ours(args):
     if rank != 0:
         return
     steps = args.steps
-    value = world * T * steps / (ms_dev / 1e3)
-    e2e_v = world * T * steps / (ms_e2e / 1e3)
+    value = chunks_world * T * steps / (ms_dev / 1e3)
+    e2e_v = chunks_world * T * steps / (ms_e2e / 1e3)
     tf_step = REF_TFLOP_PER_STEP.get(T)
     cpu = cpu_baseline(args) if world == 1 and not args.no_cpu else None
     line = {
         "metric": "frame-steps/s", "value": round(value, 3), "unit": "frame-steps/s", "n_gpus": world, "steps": steps,
-        "warmup": args.warmup, "ms_per_step": round(ms_dev / steps, 3), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "warmup": args.warmup, "ms_per_step": round(ms_dev / steps, 3), "higher_is_better": True,
+        "scaling": "weak" if chunks_world == world else "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": f"Seva 1.3B random-init, T={T} @{h * 8}x{w * 8} (latent {h}x{w}), Euler-EDM step with "
                                f"MultiviewCFG (CFG batch {2 * T}), configs[1]",
-                   "parallelism": f"dp{world} (one independent T-frame chunk per GPU)" if world > 1 else "single GPU",
+                   "parallelism": par_desc,
                    "l2": "activations per step (>2 GB) exceed the 126 MB L2; no explicit flush"},
         "e2e": {"value": round(e2e_v, 3), "unit": "frame-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e / steps, 3)},
         "gpu_launches": eng.n_launch * steps + 4 * steps,
         "clocks": clk, "roofline": roof,
-        "step_tflops": round(tf_step * steps / (ms_dev / 1e3), 1) if tf_step else None,
-        "step_frac_of_peak": round(tf_step * steps / (ms_dev / 1e3) / peaks["tf_sustained"], 4) if tf_step else None,
+        "step_tflops": round(chunks_world * tf_step * steps / (ms_dev / 1e3), 1) if tf_step else None,
+        "step_frac_of_peak": round(chunks_world * tf_step * steps / (ms_dev / 1e3) / peaks["tf_sustained"] / world, 4)
+        if tf_step else None,
         "kernels": kernels,
     }
     if cpu is not None:
@@ -340,6 +359,8 @@ if __name__ == "__main__":
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--T", type=int, default=21)
     ap.add_argument("--size", type=int, default=72)
+    ap.add_argument("--parallel", default="chunks", choices=["chunks", "cfg", "frames"],
+                    help="how N > 1 GPUs are used (see run_ours); the driver's scaling run uses the default")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--dump-launches", default=None, help="write per-launch CUDA-event timings (JSON) here")
     a = ap.parse_args()
