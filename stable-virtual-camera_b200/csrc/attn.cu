@@ -36,6 +36,7 @@ constexpr int kAttnCtrl = 1024;
 constexpr int kAttnSmem = kAttnCtrl + 1024 + (2 + kRing) * kTileBytes;
 constexpr int kRegsLow = 56;             // TMA / MMA / allocator warpgroup
 constexpr int kRegsHigh = 224;           // softmax warpgroups
+constexpr int kPingDefault = 0;          // exp-phase ping-pong between the two Q tiles' softmax warps
 constexpr int kEmuDefault = 4;           // pairs out of every 16 whose exp2 runs on the FMA pipe
 
 struct AttnArgs {
@@ -94,10 +95,21 @@ __device__ __forceinline__ unsigned long long exp2_poly2(unsigned long long x2) 
   return pack2u(r0, r1);
 }
 
+// ex2 that keeps its place relative to the exp-phase token (volatile asm statements are not reordered among themselves)
+__device__ __forceinline__ float ex2_pinned(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// Named-barrier token that serialises the exponential phases of the two warps sharing an SM sub-partition (warp w of
+// Q tile 0 and warp w + 4 of Q tile 1): one is on the MUFU unit while the other loads S and reduces the row maximum.
+__device__ __forceinline__ void token_wait(uint32_t id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void token_give(uint32_t id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+
 __device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 
 // P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; accumulates the row sum
-template <int kEmu>
+template <int kEmu, bool kPin>
 __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long sl2_2,
                                           unsigned long long negm_2, uint32_t (&pk)[16],
                                           unsigned long long& sum2) {
@@ -108,7 +120,7 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
     if (((t + 1) * kEmu) / 16 != (t * kEmu) / 16) {  // evenly spread, compile-time
       p2 = exp2_poly2(x2);
     } else {
-      p2 = pack2f(fast_exp2(lo2f(x2)), fast_exp2(hi2f(x2)));
+      p2 = kPin ? pack2f(ex2_pinned(lo2f(x2)), ex2_pinned(hi2f(x2))) : pack2f(fast_exp2(lo2f(x2)), fast_exp2(hi2f(x2)));
     }
     sum2 = fadd2(sum2, p2);
     pk[t] = pack_bf16x2(lo2f(p2), hi2f(p2));
@@ -116,9 +128,10 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
 }
 
 // One key block of the online softmax for this thread's row.
-template <bool kTail, int kEmu>
+template <bool kTail, int kEmu, bool kPing>
 __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree,
                                              uint32_t bar_pv, float sl2, int kv_valid, int j, int lane,
+                                             uint32_t tok_mine, uint32_t tok_other, bool give,
                                              float& m_run, float& l_run) {
   uint32_t s[128];
   tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
@@ -170,16 +183,18 @@ __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t 
   const unsigned long long sl2_2 = pack2f(sl2, sl2);
   const unsigned long long negm_2 = pack2f(-m_run, -m_run);
   unsigned long long sum2 = 0ull;
+  if (kPing) token_wait(tok_mine);
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     uint32_t pk[16];
-    chunk_exp<kEmu>(&s[32 * c], sl2_2, negm_2, pk, sum2);
+    chunk_exp<kEmu, kPing>(&s[32 * c], sl2_2, negm_2, pk, sum2);
+    if (kPing && c == 3 && give) token_give(tok_other);
     tmem_st16(tP + 16 * c, pk);
   }
   l_run += lo2f(sum2) + hi2f(sum2);
 }
 
-template <int kEmu>
+template <int kEmu, bool kPing>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -349,14 +364,18 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const float sl2 = a.scale_log2;
     float m_run = -INFINITY;  // running max of s*scale*log2(e) (possibly stale by < 8)
     float l_run = 0.0f;
+    const uint32_t tok_mine = 1 + 2 * quarter + i, tok_other = 1 + 2 * quarter + (i ^ 1);
+    if (kPing && i == 1) token_give(tok_other);  // tile 0 takes the first turn
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(bar_s + 8 * i, j & 1);
       tc_fence_after();
       const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
       if (kv_valid >= 128)
-        softmax_step<false, kEmu>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, m_run, l_run);
+        softmax_step<false, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, tok_mine,
+                                         tok_other, i == 0 || j + 1 < nkv, m_run, l_run);
       else
-        softmax_step<true, kEmu>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, m_run, l_run);
+        softmax_step<true, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, tok_mine,
+                                        tok_other, i == 0 || j + 1 < nkv, m_run, l_run);
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
@@ -443,25 +462,42 @@ extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* 
   a.ldo = ldo;
   a.bso = bso;
   a.scale_log2 = scale * 1.4426950408889634f;
-  // developer knob: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 selects the fraction (n/16) of exponentials on the FMA pipe
-  static int emu = -1;
+  // developer knobs: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_PING = 0 / 1
+  static int emu = -1, ping = kPingDefault;
   if (emu < 0) {
     const char* e = getenv("SEVA_ATTN_EMU");
     emu = e ? atoi(e) : kEmuDefault;
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-    SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
+    const char* pg = getenv("SEVA_ATTN_PING");
+    if (pg) ping = atoi(pg);
   }
   dim3 grid((Lq + 255) / 256, Hh, B);
-  switch (emu) {
-    case 0: attn_kernel<0><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
-    case 2: attn_kernel<2><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
-    case 6: attn_kernel<6><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
-    case 8: attn_kernel<8><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
-    default: attn_kernel<4><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a); break;
+#define SEVA_ATTN_LAUNCH(E, P)                                                                               \
+  {                                                                                                          \
+    static bool attr = false;                                                                                \
+    if (!attr) {                                                                                             \
+      SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<E, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem)); \
+      attr = true;                                                                                           \
+    }                                                                                                        \
+    attn_kernel<E, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);                          \
   }
+  if (ping) {
+    switch (emu) {
+      case 0: SEVA_ATTN_LAUNCH(0, true) break;
+      case 2: SEVA_ATTN_LAUNCH(2, true) break;
+      case 6: SEVA_ATTN_LAUNCH(6, true) break;
+      case 8: SEVA_ATTN_LAUNCH(8, true) break;
+      default: SEVA_ATTN_LAUNCH(4, true) break;
+    }
+  } else {
+    switch (emu) {
+      case 0: SEVA_ATTN_LAUNCH(0, false) break;
+      case 2: SEVA_ATTN_LAUNCH(2, false) break;
+      case 6: SEVA_ATTN_LAUNCH(6, false) break;
+      case 8: SEVA_ATTN_LAUNCH(8, false) break;
+      default: SEVA_ATTN_LAUNCH(4, false) break;
+    }
+  }
+#undef SEVA_ATTN_LAUNCH
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
