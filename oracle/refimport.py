@@ -30,3 +30,32 @@ def import_reference():
     import seva.sampling as sampling
 
     return types.SimpleNamespace(model=model, sampling=sampling, geometry=geometry)
+
+
+def import_eval():
+    """`seva.eval` (chunk planner / scene loop bookkeeping).  Needs attribute-bearing stand-ins for colorama and
+    stubs for gradio / imageio / torchvision / PIL when those are absent."""
+    import_reference()
+    col = sys.modules.get("colorama")
+    if col is not None and not hasattr(col, "Fore"):
+        col.Fore = types.SimpleNamespace(RED="", GREEN="")
+        col.Style = types.SimpleNamespace(RESET_ALL="")
+        col.init = lambda **k: None
+    gr = sys.modules.get("gradio")
+    if gr is not None and not hasattr(gr, "Progress"):
+        gr.Progress = type("Progress", (), {})
+    iio = sys.modules.get("imageio")
+    if iio is not None and not hasattr(iio, "v3"):
+        iio.v3 = sys.modules["imageio.v3"]
+    for name in ("torchvision", "torchvision.transforms", "torchvision.transforms.functional", "PIL", "PIL.Image"):
+        if name not in sys.modules:
+            try:
+                __import__(name)
+            except Exception:
+                sys.modules[name] = types.ModuleType(name)
+                parent, _, child = name.rpartition(".")
+                if parent:
+                    setattr(sys.modules[parent], child, sys.modules[name])
+    import seva.eval as E
+
+    return E
