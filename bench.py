@@ -307,6 +307,106 @@ def run_ours(args):
 
 
 # ----------------------------------------------------------------------------------------------------
+def arc_cameras(n, seed):
+    """[n,4,4] c2w along a jittered arc (synthetic trajectory for the scene workload)."""
+    g = torch.Generator().manual_seed(seed)
+    t = torch.linspace(0, 1, n)
+    yaw = 1.5 * t + 0.05 * torch.randn(n, generator=g)
+    c2w = torch.eye(4).repeat(n, 1, 1)
+    c2w[:, 0, 0], c2w[:, 0, 2], c2w[:, 2, 0], c2w[:, 2, 2] = torch.cos(yaw), torch.sin(yaw), -torch.sin(yaw), torch.cos(yaw)
+    c2w[:, :3, 3] = torch.stack([2 * torch.sin(2.5 * t), 0.3 * torch.cos(4 * t), -2 * torch.cos(2.5 * t)], 1) \
+        + 0.05 * torch.randn(n, 3, generator=g)
+    return c2w
+
+
+def run_scene_bench(args):
+    """BASELINE.json configs[2]: two-pass chunked sampling, 1 input -> 80 target views, T=21 windows (1 anchor window +
+    7 target windows = 8 runs x 21 frames x 50 steps = 8400 frame-steps), scheduled over the N GPUs by
+    seva_b200.scene: the anchor window model-parallel over all ranks (CFG halves x frame shards), the 7 independent
+    target windows dealt round-robin.  VAE / CLIP are outside the path: identity codec, fixed token projection."""
+    import numpy as np
+
+    from seva_b200 import dist as D
+    from seva_b200 import planner as P
+    from seva_b200 import sampling as S
+    from seva_b200 import scene as SC
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    where = SC.Rank()
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+        topo = D.Topology(world, rank, cfg=2, sp=world // 2)
+        groups = D.build_groups(topo)
+        where = SC.Rank(rank=rank, world=world, chain_frames=groups["frames"],
+                        chain_guider=lambda g: D.CFGSplit(g, groups["cfg"], half=topo.half))
+    model, _ = build_model(dev)
+    T, hh, n_targets = args.T, args.size, 80
+    f = 0.5 / math.tan(0.5 * 0.9424777960769379)
+    Kn = lambda n: torch.tensor([[f, 0, 0.5], [0, f, 0.5], [0, 0, 1.0]]).repeat(n, 1, 1)
+    traj, inp = arc_cameras(n_targets, 3), arc_cameras(1, 4)
+    opts = {"chunk_strategy": "interp", "chunk_strategy_first_pass": "gt-nearest", "cfg": [3.0, 2.0]}
+    version = {"T": [T, T], "options": opts}
+    prior = P.infer_prior_inds(traj, P.infer_prior_stats([T, T], 1, n_targets, version), [], opts)
+    sc = SC.Scene(torch.randn(1, 4, hh, hh, generator=torch.Generator().manual_seed(5)), inp, Kn(1), traj, Kn(n_targets),
+                  [0], list(range(1, n_targets + 1)), traj[prior], Kn(len(prior)), [int(i) + 1 for i in prior])
+    plan = SC.plan_scene(sc, version["T"], opts, task="img2trajvid", use_traj_prior=True)
+    n_runs = sum(len(p.windows) for p in plan.passes)
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device=dev)
+
+    def samplers(steps):
+        def make(T_, wrap):
+            g = S.MultiviewCFG(1.2)
+            return S.EulerEDMSampler(disc, wrap(g) if wrap else g, num_steps=steps, s_churn=0.0, s_tmin=0.0,
+                                     s_tmax=999.0, s_noise=1.0, verbose=False, device=dev)
+        return make
+
+    def sync():
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    torch.manual_seed(1234)
+    SC.run_scene(sc, plan, model, denoiser, samplers(2), where=where, generator=torch.Generator().manual_seed(7),
+                 device=dev)  # warm-up: builds every plan (sharded and unsharded), 2 steps per run
+    clocks = ClockSampler(local)
+    clocks.start()
+    sync()
+    t0 = time.time()
+    out = SC.run_scene(sc, plan, model, denoiser, samplers(50), where=where,
+                       generator=torch.Generator().manual_seed(7), device=dev)
+    sync()
+    secs = time.time() - t0
+    clk = clocks.stop()
+    if world > 1:
+        import torch.distributed as dist
+
+        t = torch.tensor([secs], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = t.item()
+    assert out.shape[0] == n_targets and torch.isfinite(out).all()
+    if rank == 0:
+        fs = n_runs * T * 50
+        print(json.dumps({
+            "metric": "frame-steps/s", "value": round(fs / secs, 3), "unit": "frame-steps/s", "n_gpus": world,
+            "steps": 50 * n_runs, "warmup": 2 * n_runs, "seconds": round(secs, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"two-pass scene, 1 input -> {n_targets} targets, T={T} @{hh * 8}x{hh * 8}: "
+                                   f"{len(plan.passes[0].windows)} anchor + {len(plan.passes[1].windows)} target windows x "
+                                   f"50 Euler-EDM steps with MultiviewCFG = {fs} frame-steps, configs[2]",
+                       "parallelism": "single GPU" if world == 1 else
+                       f"anchor window over cfg2 x frames{world // 2}; target windows round-robin over {world} GPUs",
+                       "timing": "host wall clock around the whole scene (barrier + synchronize both sides), max over ranks"},
+            "clocks": clk, "latent_checksum": round(float(out.double().abs().mean()), 6)}))
+
+
 def cpu_step_sample(T, h, w, threads):
     """One Euler-EDM step of the oracle port (plain PyTorch fp32) on the host cores; returns seconds."""
     from oracle import seva_oracle as O
@@ -377,6 +477,8 @@ if __name__ == "__main__":
     ap.add_argument("--size", type=int, default=72)
     ap.add_argument("--parallel", default="chunks", choices=["chunks", "cfg", "frames"],
                     help="how N > 1 GPUs are used (see run_ours); the driver's scaling run uses the default")
+    ap.add_argument("--workload", default="step", choices=["step", "scene"],
+                    help="step: one Euler-EDM step of configs[1] (the driver's contract); scene: configs[2] end to end")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--dump-launches", default=None, help="write per-launch CUDA-event timings (JSON) here")
     a = ap.parse_args()
@@ -385,4 +487,4 @@ if __name__ == "__main__":
     else:
         if not torch.cuda.is_available():
             raise SystemExit("bench.py --impl ours needs a B200: the product path has no CPU fallback")
-        run_ours(a)
+        run_scene_bench(a) if a.workload == "scene" else run_ours(a)

@@ -70,6 +70,22 @@ def main():
     n_err = sum("error" in r for r in out["chunks"])
     print(f"chunk cases: {len(out['chunks'])} ({n_err} raise in the reference)")
 
+    # get_value_dict (eval.py:1152-1215): camera normalisation + ray map of one window, reference on CPU
+    import torch
+    vd = []
+    for seed, T, far in ((11, 6, False), (12, 5, True)):
+        allc = PC.cameras(30, seed)
+        if far:
+            allc[3, :3, 3] += 1e4  # an outlier camera: excluded from the centring mean by the quantile rule
+        idx = list(range(0, 30, 30 // T))[:T]
+        f = 0.5 / np.tan(0.5 * 0.9424777960769379)
+        Ks = torch.tensor([[f, 0, 0.5], [0, f, 0.5], [0, 0, 1.0]], dtype=torch.float32).repeat(T, 1, 1)
+        v = E.get_value_dict(torch.zeros(T, 3, 128, 128), torch.zeros(T, 3, 128, 128), [0], allc[idx].clone(), Ks,
+                             list(range(T)), all_c2ws=allc, camera_scale=2.0)
+        vd.append(dict(seed=seed, T=T, far=far, idx=idx, c2w=v["c2w"].tolist(),
+                       plucker=v["plucker_coordinate"].tolist()))
+    out["value_dict"] = vd
+
     path = os.path.join(ROOT, "tests", "golden", "planner.json")
     with open(path, "w") as f:
         json.dump(out, f, separators=(",", ":"))

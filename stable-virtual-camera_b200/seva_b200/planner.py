@@ -2,7 +2,7 @@
 
 The caller of the sampling path (``run_one_scene``, seva/eval.py:1324-1974) cuts a scene into runs of T frames.
 This module restates that integer bookkeeping -- bit-exact against the reference on the committed fixtures
-(tests/golden/planner.json, generated by oracle/gen_golden_planner.py from the real reference):
+(tests/golden/planner.json, generated from the real reference by the committed golden-vector script):
 
 * ``pad_indices`` / ``assemble``                      eval.py:44-96
 * ``infer_prior_stats`` / ``infer_prior_inds``        eval.py:344-453
