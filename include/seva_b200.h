@@ -69,6 +69,9 @@ typedef struct SevaGemm {
   int32_t Hp, Wp;
   int32_t bn;          /* N tile (multiple of 32, <= 256; GEGLU: multiple of 64); 0 = choose            */
   int32_t cluster;     /* 0 = choose; 1 = one CTA per 128-row tile; 2 = CTA pair per 256-row tile      */
+  int32_t reverse;     /* 1: process (and write) row tiles from the last to the first.  L2-aware traversal:
+                        * a consumer that walks a tensor in the OPPOSITE order to the kernel that last touched
+                        * it finds the most recent ~100 MB still in the 126 MB L2.  Results are identical.   */
 } SevaGemm;
 int seva_gemm_bf16(const SevaGemm* g, void* stream);
 /* N tile seva_gemm_bf16 will use for (N, geglu) when g->bn == 0 (weights for geglu are packed against it). */
@@ -92,9 +95,15 @@ int seva_timemix_attn_kv(const void* q, const void* k, const void* v, void* out,
                          float scale, void* stream);
 
 /* ---- normalisation ---------------------------------------------------------------------------- */
-/* Per-(image, channel) sum and sum of squares over rpi rows: sums[n, c, 0:2] (fp32, zeroed inside). */
+/* `reverse` (here and in seva_layernorm): 1 = walk the rows from the last to the first (see SevaGemm.reverse).
+ * Per-(image, channel) sum and sum of squares over rpi rows: sums[n, c, 0:2] (fp32), deterministic (no atomics
+ * on the data).  `sums` is a 16-byte aligned buffer of seva_groupnorm_stats_floats(Nimg, rpi, C) floats: the
+ * [Nimg, C, 2] totals first (what seva_groupnorm_apply reads), then per-block partials and one ticket per image.
+ * The buffer must be ZERO when first used; every launch leaves the tickets zero again, so it can be reused by
+ * launches of the same (Nimg, rpi, C) on one stream without clearing. */
+int64_t seva_groupnorm_stats_floats(int32_t Nimg, int32_t rpi, int32_t C);
 int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
-                         float* sums, void* stream);
+                         float* sums, int32_t reverse, void* stream);
 typedef struct SevaGNApply {
   const void* x; int64_t ldx;     /* bf16 input, zero-bordered flat (in_padded=1) or compact rows        */
   void* y; int64_t ldy;           /* bf16 output                                                          */
@@ -107,11 +116,12 @@ typedef struct SevaGNApply {
   const float* dense;             /* optional fp32 [Nimg, H*Wd, 6] resized Plucker map, or NULL           */
   const float* dense_w;           /* fp32 [2C, 6] (scale rows first, then shift rows)                     */
   const float* dense_b;           /* fp32 [2C]                                                            */
+  int32_t reverse;                /* 1: walk images / pixels from the last to the first (see SevaGemm.reverse) */
 } SevaGNApply;
 int seva_groupnorm_apply(const SevaGNApply* p, void* stream);
 /* y[m, :] = LayerNorm(x[m, :]) * gamma + beta, eps inside sqrt; bf16 in/out, fp32 statistics. */
 int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, const float* gamma,
-                   const float* beta, int32_t M, int32_t C, float eps, void* stream);
+                   const float* beta, int32_t M, int32_t C, float eps, int32_t reverse, void* stream);
 
 /* ---- camera geometry --------------------------------------------------------------------------- */
 /* Plucker ray map.  w2c [T,4,4], w2c_src [4,4], Kpix [T,3,3] intrinsics already in latent-pixel units

@@ -48,6 +48,7 @@ struct GemmArgs {
   long long ldo;
   int out_fp32, geglu, out_map, H, Wd, mask_border, Hp, Wp;
   int dbg;
+  int reverse;  // 1: walk the tile list backwards (L2-aware traversal, see seva_b200.h)
   int fast;  // 1: bf16 output, N % 32 == 0 and 16-byte aligned pointers/strides -> coalesced epilogue
 };
 
@@ -278,8 +279,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         // one elected lane issues the TMA instructions
       uint32_t it_g = 0, s = 0, ph = 0;
       for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters) {
-        const int m0 = (tile / a.n_tiles) * (BM * kCtas) + rank * BM;
-        const int n0 = (tile % a.n_tiles) * a.bn + rank * b_rows;
+        const int pt = a.reverse ? a.num_tiles - 1 - tile : tile;
+        const int m0 = (pt / a.n_tiles) * (BM * kCtas) + rank * BM;
+        const int n0 = (pt % a.n_tiles) * a.bn + rank * b_rows;
         for (int tap = 0; tap < a.ntaps; ++tap) {
           int off = 0;
           if (a.ntaps == 9) off = (tap / 3 - 1) * a.tap_wp + (tap % 3 - 1);
@@ -373,6 +375,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     auto fetch_cb = [&](int tile_) -> float4 {
       float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
       if (!has_cb || tile_ >= a.num_tiles) return r;
+      if (a.reverse) tile_ = a.num_tiles - 1 - tile_;
       int o = 4 * lane, twin = 0;
       if (a.geglu && o >= 64) { o -= 64; twin = a.bn / 2; }
       if (o >= seg_len || (a.geglu && 4 * lane >= 128)) return r;
@@ -403,8 +406,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t tl = 0;
     for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
       const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
-      const int tile_n = tile % a.n_tiles;
-      const int m0 = (tile / a.n_tiles) * (BM * kCtas) + rank * BM;
+      const int pt = a.reverse ? a.num_tiles - 1 - tile : tile;
+      const int tile_n = pt % a.n_tiles;
+      const int m0 = (pt / a.n_tiles) * (BM * kCtas) + rank * BM;
       const int n0 = tile_n * a.bn;
       const int m = m0 + row_in_tile;
       if (has_cb) {
@@ -629,6 +633,7 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.mask_border = g->mask_border;
   a.Hp = g->Hp;
   a.Wp = g->Wp;
+  a.reverse = g->reverse != 0;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   {
     static int dbg = -1;

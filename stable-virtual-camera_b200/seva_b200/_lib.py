@@ -25,6 +25,7 @@ class SevaGemm(C.Structure):
         ("out", c_void_p), ("ldo", c_i64),
         ("out_fp32", c_int), ("geglu", c_int), ("out_map", c_int), ("H", c_int), ("Wd", c_int),
         ("mask_border", c_int), ("Hp", c_int), ("Wp", c_int), ("bn", c_int), ("cluster", c_int),
+        ("reverse", c_int),
     ]
 
 
@@ -34,7 +35,7 @@ class SevaGNApply(C.Structure):
         ("sums", c_void_p), ("gamma", c_void_p), ("beta", c_void_p),
         ("Nimg", c_int), ("H", c_int), ("Wd", c_int), ("C", c_int), ("groups", c_int),
         ("eps", c_float), ("in_padded", c_int), ("out_padded", c_int), ("silu", c_int),
-        ("dense", c_void_p), ("dense_w", c_void_p), ("dense_b", c_void_p),
+        ("dense", c_void_p), ("dense_w", c_void_p), ("dense_b", c_void_p), ("reverse", c_int),
     ]
 
 
@@ -52,9 +53,10 @@ _PROTOS = {
     "seva_attn_fwd": [c_void_p] * 4 + [c_int] * 4 + [c_i64] * 8 + [c_float, c_void_p],
     "seva_timemix_attn": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_i64, c_i64, c_float, c_void_p],
     "seva_timemix_attn_kv": [c_void_p] * 4 + [c_int] * 5 + [c_i64] * 3 + [c_float, c_void_p],
-    "seva_groupnorm_stats": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_void_p],
+    "seva_groupnorm_stats_floats": [c_int, c_int, c_int],
+    "seva_groupnorm_stats": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_int, c_void_p],
     "seva_groupnorm_apply": [C.POINTER(SevaGNApply), c_void_p],
-    "seva_layernorm": [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
+    "seva_layernorm": [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p],
     "seva_plucker": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     "seva_resize_bilinear_ac": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "seva_multiview_scale": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_void_p, c_void_p, c_int,
@@ -99,6 +101,7 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.argtypes = argtypes
         fn.restype = C.c_int
+    lib.seva_groupnorm_stats_floats.restype = C.c_int64
     lib.seva_last_error.argtypes = []
     lib.seva_last_error.restype = C.c_char_p
     _lib = lib

@@ -13,6 +13,7 @@ loop of foreign calls with constant arguments (and is CUDA-graph capturable).
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -118,6 +119,7 @@ class FrameShard:
         self.counts = [b - a for a, b in self.parts]
         if min(self.counts) < 1:
             raise SevaB200Error(f"{T_total} frames cannot be split over {self.size} ranks (a rank would own none)")
+        self._stage: dict = {}   # padded all-gather staging buffers per (B, rows, C)
 
     @property
     def T_local(self) -> int:
@@ -130,12 +132,30 @@ class FrameShard:
 
     def gather(self, out: torch.Tensor, loc: torch.Tensor, B: int, rows_per_frame: int) -> None:
         """out [B*T_total*rpf, C] <- every rank's loc [B*T_r*rpf, C], frames in global order per batch element."""
-        from .dist import allgather_rows
+        import torch.distributed as dist
 
-        cnt = [c * rows_per_frame for c in self.counts]
         nl, nf = self.T_local * rows_per_frame, self.T_total * rows_per_frame
-        for b in range(B):
-            allgather_rows(out[b * nf:(b + 1) * nf], cnt, loc[b * nl:(b + 1) * nl], self.group)
+        if B == 1 and len(set(self.counts)) == 1:
+            dist.all_gather_into_tensor(out, loc, group=self.group)
+            return
+        # ONE collective per call whatever the split: every rank contributes a block padded to the largest share
+        # ([B, cmax * rpf, C]); the P blocks are then scattered to their frame ranges with one strided copy each.
+        # (A broadcast per rank and batch element -- 2 P B launches per site, 23 sites per forward -- cost more
+        # than the attention it feeds at 8 GPUs.)
+        cmax = max(self.counts) * rows_per_frame
+        C_ = loc.shape[1]
+        key = (B, cmax, C_, loc.dtype, loc.device)
+        st = self._stage.get(key)
+        if st is None:
+            st = (torch.zeros(B, cmax, C_, dtype=loc.dtype, device=loc.device),
+                  torch.empty(self.size, B, cmax, C_, dtype=loc.dtype, device=loc.device))
+            self._stage[key] = st
+        send, recv = st
+        send[:, :nl].copy_(loc.view(B, nl, C_))
+        dist.all_gather_into_tensor(recv, send, group=self.group)
+        o = out.view(B, nf, C_)
+        for r, (a, b) in enumerate(self.parts):
+            o[:, a * rows_per_frame:b * rows_per_frame].copy_(recv[r, :, :(b - a) * rows_per_frame])
 
 
 class _FrameGather:
@@ -180,6 +200,8 @@ class Engine:
         self.bufs: dict = {}
         self.n_launch = 0
         self.gemv_groups: dict = {}
+        self.walk: dict = {}    # storage -> direction (True = descending rows) of the last kernel that touched it
+        self.zigzag = os.environ.get("SEVA_ZIGZAG", "0") == "1"  # measured: no gain at T=21
         self.timing_sink: list | None = None  # set by bench.py to collect per-launch CUDA events
 
         # static inputs
@@ -208,6 +230,22 @@ class Engine:
             self.bufs[key] = t
         return t
 
+    # L2-aware traversal (include/seva_b200.h, SevaGemm.reverse): a kernel walks its main input in the opposite
+    # row order to the kernel that last touched that buffer, so the most recently written / read ~100 MB are found
+    # in the 126 MB L2 instead of DRAM.  ``walk`` tracks the last direction per underlying storage.
+    def _dir(self, src, *touched) -> bool:
+        key = src.untyped_storage().data_ptr()
+        rev = (not self.walk.get(key, False)) if self.zigzag else False
+        for t in (src,) + touched:
+            if t is not None:
+                self.walk[t.untyped_storage().data_ptr()] = rev
+        return rev
+
+    def _touch_forward(self, *tensors) -> None:
+        for t in tensors:
+            if t is not None:
+                self.walk[t.untyped_storage().data_ptr()] = False
+
     def add(self, fn, *args, flops: float = 0.0, nbytes: float = 0.0, tag: str = ""):
         """Append one kernel launch; flops / nbytes are the ALGORITHMIC work of the reference op it replaces
         (2*MAC for Linear/conv on unpadded pixels, 4*B*H*Lq*Lk*D for attention, activation bytes for norms)."""
@@ -228,7 +266,8 @@ class Engine:
                           rowbias_ptr=None if rowbias is None else rowbias.data_ptr(), rowbias_rpi=rowbias_rpi,
                           residual_ptr=None if residual is None else residual.data_ptr(),
                           ldr=0 if residual is None else residual.stride(0), out_fp32=out_fp32, geglu=geglu,
-                          out_map=out_map, H=H, Wd=Wd, mask_border=mask_border, Hp=Hp, Wp=Wp, bn=bn)
+                          out_map=out_map, H=H, Wd=Wd, mask_border=mask_border, Hp=Hp, Wp=Wp, bn=bn,
+                          reverse=self._dir(A, out))
         self.keep += [g, A, W, out, bias, rowbias, residual]
         m_alg = M if alg_rows is None else alg_rows
         kk = (A.shape[1] if Kc is None else Kc) if alg_k is None else alg_k
@@ -246,23 +285,24 @@ class Engine:
         """GroupNorm: stats launch (+ memset inside) and apply launch."""
         H, Wd = self.HW[l]
         rpi = (H + 2) * (Wd + 2) if in_padded else H * Wd
-        sums = self.buf("gn_sums", self.N, 2 * C_, F32)
+        sums = self.buf("gn_sums", ops.gn_stats_floats(self.N, rpi, C_), 1, F32)  # zero-initialised, self-resetting
         act = 2.0 * self.N * H * Wd * C_
         self.add(self.lib.seva_groupnorm_stats, x.data_ptr(), x.stride(0), self.N, rpi, C_, sums.data_ptr(),
-                 nbytes=act, tag=f"gn_stats HW{H * Wd} C{C_}")
+                 int(self._dir(x)), nbytes=act, tag=f"gn_stats HW{H * Wd} C{C_}")
         pa = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
                                sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(),
                                n_img=self.N, H=H, Wd=Wd, Cc=C_, groups=32, eps=eps, in_padded=in_padded,
                                out_padded=out_padded, silu=silu,
                                dense_ptr=None if dense is None else dense.data_ptr(),
                                dense_w_ptr=None if dense_w is None else dense_w.data_ptr(),
-                               dense_b_ptr=None if dense_b is None else dense_b.data_ptr())
+                               dense_b_ptr=None if dense_b is None else dense_b.data_ptr(),
+                               reverse=self._dir(x, out))
         self.keep += [pa, x, out, gamma, beta, dense, dense_w, dense_b]
         self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act, tag=f"gn_apply HW{H * Wd} C{C_} d{int(dense is not None)}")
 
     def ln(self, x, nrm, out):
         self.add(self.lib.seva_layernorm, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0),
-                 nrm["g"].data_ptr(), nrm["b"].data_ptr(), x.shape[0], x.shape[1], nrm["eps"],
+                 nrm["g"].data_ptr(), nrm["b"].data_ptr(), x.shape[0], x.shape[1], nrm["eps"], int(self._dir(x, out)),
                  nbytes=4.0 * x.shape[0] * x.shape[1], tag=f"layernorm M{x.shape[0]} C{x.shape[1]}")
         self.keep += [x, out]
 
@@ -420,6 +460,7 @@ class Engine:
         Ho, Wo = self.HW[l + 1]
         col = self.buf(f"im2col_{l}", self.N * Ho * Wo, 9 * m.channels)
         self.add(self.lib.seva_im2col3x3_s2, x.data_ptr(), x.stride(0), col.data_ptr(), self.N, H, Wd, m.channels)
+        self._touch_forward(x, col)
         self.keep += [x]
         self.gemm(col, w["w"], out, bias=w["b"], out_map=1, H=Ho, Wd=Wo)
 
@@ -430,6 +471,7 @@ class Engine:
         up = self.buf(f"up_{l - 1}", self.rows_p(l - 1), m.channels)
         self.add(self.lib.seva_upsample2x_pad, x.data_ptr(), x.stride(0), up.data_ptr(), up.stride(0), self.N, H,
                  Wd, m.channels)
+        self._touch_forward(x, up)
         self.keep += [x]
         self.conv3x3(up, l - 1, w["w"], w["b"], out)
 
@@ -484,6 +526,7 @@ class Engine:
                      heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
                      Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
                      tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
+            self._touch_forward(q, kvf, o)
         else:
             self.gemm(a, w["s_attn1"]["wqkv"], qkv)
             ld = qkv.stride(0)
@@ -492,6 +535,7 @@ class Engine:
                      ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
                      flops=4.0 * bat * heads * Lseq * Lseq * 64,
                      tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
+            self._touch_forward(qkv, o)
         x1 = self.buf(f"tk_x1_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
@@ -514,11 +558,13 @@ class Engine:
                      o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
                      flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
                      tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
+            self._touch_forward(q, kvf, o)
         else:
             self.gemm(a, w["t_attn1"]["wqkv"], qkv)
             self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
                      o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
                      tag=f"timemix BS{B * S} H{heads}")
+            self._touch_forward(qkv, o)
         y2 = self.buf(f"tk_y2_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
@@ -562,6 +608,7 @@ class Engine:
         self.add(self.lib.seva_attn_fwd, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), bat, heads, Lseq,
                  self.L, C_, C_, C_, C_, Lseq * C_, self.L * C_, self.L * C_, Lseq * C_, 0.125,
                  flops=4.0 * bat * heads * Lseq * self.L * 64, tag="attn_cross")
+        self._touch_forward(q, o)
         self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin)
 
     # ---- execution ------------------------------------------------------------------------------

@@ -43,7 +43,7 @@ def pick_bn(N: int, geglu: bool = False) -> int:
 # ------------------------------------------------------------------------------------------------
 def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1, tap_wp=0, bias_ptr=None,
               rowbias_ptr=None, rowbias_rpi=0, residual_ptr=None, ldr=0, out_fp32=False, geglu=False,
-              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, cluster=0) -> SevaGemm:
+              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, cluster=0, reverse=False) -> SevaGemm:
     g = SevaGemm()
     g.A, g.lda, g.a_rows = A_ptr, lda, a_rows
     g.W, g.ldw = W_ptr, ldw
@@ -53,6 +53,7 @@ def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1
     g.out, g.ldo = out_ptr, ldo
     g.out_fp32, g.geglu, g.out_map, g.H, g.Wd = int(out_fp32), int(geglu), out_map, H, Wd
     g.mask_border, g.Hp, g.Wp, g.bn, g.cluster = int(mask_border), Hp, Wp, bn, cluster
+    g.reverse = int(reverse)
     return g
 
 
@@ -62,7 +63,8 @@ def run_gemm(g: SevaGemm) -> None:
 
 def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *, out: torch.Tensor | None = None,
            residual: torch.Tensor | None = None, rowbias: torch.Tensor | None = None, rowbias_rpi: int = 0,
-           geglu: bool = False, out_fp32: bool = False, bn: int = 0, cluster: int = 0) -> torch.Tensor:
+           geglu: bool = False, out_fp32: bool = False, bn: int = 0, cluster: int = 0,
+           reverse: bool = False) -> torch.Tensor:
     """out = A @ W.T (+bias) (+rowbias[row // rpi]) (+residual); A [M,K] bf16, W [N,K] bf16 (row strides free)."""
     _req(A, torch.bfloat16, "A"), _req(W, torch.bfloat16, "W")
     M, K = A.shape
@@ -74,7 +76,7 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *
                   Kc=K, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias), rowbias_ptr=_p(rowbias),
                   rowbias_rpi=rowbias_rpi, residual_ptr=_p(residual),
                   ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, geglu=geglu, bn=bn,
-                  cluster=cluster)
+                  cluster=cluster, reverse=reverse)
     run_gemm(g)
     return out
 
@@ -82,7 +84,7 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *
 def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None, N_img: int, H: int, Wd: int, *,
                    out: torch.Tensor | None = None, residual: torch.Tensor | None = None,
                    rowbias: torch.Tensor | None = None, out_fp32: bool = False, bn: int = 0,
-                   cluster: int = 0) -> torch.Tensor:
+                   cluster: int = 0, reverse: bool = False) -> torch.Tensor:
     """3x3/s1/p1 conv on a zero-bordered flat image x [N_img*(H+2)*(Wd+2), Cin]; W9 [Cout, 9*Cin] tap-major."""
     _req(x, torch.bfloat16, "x"), _req(W9, torch.bfloat16, "W9")
     rows, Cin = x.shape
@@ -95,7 +97,7 @@ def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None,
                   N=Cout, Kc=Cin, ntaps=9, tap_wp=Wp, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias),
                   rowbias_ptr=_p(rowbias), rowbias_rpi=Hp * Wp, residual_ptr=_p(residual),
                   ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, mask_border=True,
-                  Hp=Hp, Wp=Wp, bn=bn, cluster=cluster)
+                  Hp=Hp, Wp=Wp, bn=bn, cluster=cluster, reverse=reverse)
     run_gemm(g)
     return out
 
@@ -165,23 +167,36 @@ def timemix_attention_kv(q: torch.Tensor, kv: torch.Tensor, B: int, Tq: int, Tk:
 # ------------------------------------------------------------------------------------------------
 # norms
 # ------------------------------------------------------------------------------------------------
-def groupnorm_stats(x: torch.Tensor, n_img: int, rpi: int, Cc: int, sums: torch.Tensor | None = None) -> torch.Tensor:
+def gn_stats_floats(n_img: int, rpi: int, Cc: int) -> int:
+    n = _lib.load().seva_groupnorm_stats_floats(n_img, rpi, Cc)
+    if n < 0:
+        raise _lib.SevaB200Error(f"seva_groupnorm_stats_floats({n_img}, {rpi}, {Cc}) failed")
+    return int(n)
+
+
+def groupnorm_stats(x: torch.Tensor, n_img: int, rpi: int, Cc: int, sums: torch.Tensor | None = None,
+                    reverse: bool = False) -> torch.Tensor:
+    """``sums``: a ZERO-initialised fp32 buffer of ``gn_stats_floats(n_img, rpi, Cc)`` elements (reusable across
+    launches of the same shape); the [n_img, Cc, 2] totals are its first elements."""
     _req(x, torch.bfloat16, "x")
     if sums is None:
-        sums = torch.empty((n_img, Cc, 2), device=x.device, dtype=torch.float32)
-    check(_lib.load().seva_groupnorm_stats(x.data_ptr(), x.stride(0), n_img, rpi, Cc, sums.data_ptr(), _stream()),
+        sums = torch.zeros(gn_stats_floats(n_img, rpi, Cc), device=x.device, dtype=torch.float32)
+    check(_lib.load().seva_groupnorm_stats(x.data_ptr(), x.stride(0), n_img, rpi, Cc, sums.data_ptr(), int(reverse),
+                                           _stream()),
           "seva_groupnorm_stats")
     return sums
 
 
 def make_gn_apply(*, x_ptr, ldx, y_ptr, ldy, sums_ptr, gamma_ptr, beta_ptr, n_img, H, Wd, Cc, groups, eps,
-                  in_padded, out_padded, silu, dense_ptr=None, dense_w_ptr=None, dense_b_ptr=None) -> SevaGNApply:
+                  in_padded, out_padded, silu, dense_ptr=None, dense_w_ptr=None, dense_b_ptr=None,
+                  reverse=False) -> SevaGNApply:
     p = SevaGNApply()
     p.x, p.ldx, p.y, p.ldy = x_ptr, ldx, y_ptr, ldy
     p.sums, p.gamma, p.beta = sums_ptr, gamma_ptr, beta_ptr
     p.Nimg, p.H, p.Wd, p.C, p.groups = n_img, H, Wd, Cc, groups
     p.eps, p.in_padded, p.out_padded, p.silu = eps, int(in_padded), int(out_padded), int(silu)
     p.dense, p.dense_w, p.dense_b = dense_ptr, dense_w_ptr, dense_b_ptr
+    p.reverse = int(reverse)
     return p
 
 
@@ -191,32 +206,33 @@ def run_gn_apply(p: SevaGNApply) -> None:
 
 def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, n_img: int, H: int, Wd: int, *, groups=32,
               eps=1e-5, in_padded=True, out_padded=True, silu=False, dense=None, dense_w=None, dense_b=None,
-              out: torch.Tensor | None = None) -> torch.Tensor:
+              out: torch.Tensor | None = None, reverse: bool = False) -> torch.Tensor:
     """GroupNorm (+SiLU, +dense modulation) of a channels-last image batch (two launches: stats, apply)."""
     _req(x, torch.bfloat16, "x")
     Cc = x.shape[1]
     rpi_in = (H + 2) * (Wd + 2) if in_padded else H * Wd
     rpi_out = (H + 2) * (Wd + 2) if out_padded else H * Wd
     assert x.shape[0] == n_img * rpi_in
-    sums = groupnorm_stats(x, n_img, rpi_in, Cc)
+    sums = groupnorm_stats(x, n_img, rpi_in, Cc, reverse=reverse)
     if out is None:
         out = torch.empty((n_img * rpi_out, Cc), device=x.device, dtype=torch.bfloat16)
     p = make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
                       sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(), n_img=n_img,
                       H=H, Wd=Wd, Cc=Cc, groups=groups, eps=eps, in_padded=in_padded, out_padded=out_padded,
-                      silu=silu, dense_ptr=_p(dense), dense_w_ptr=_p(dense_w), dense_b_ptr=_p(dense_b))
+                      silu=silu, dense_ptr=_p(dense), dense_w_ptr=_p(dense_w), dense_b_ptr=_p(dense_b),
+                      reverse=not reverse)
     run_gn_apply(p)
     return out
 
 
 def layernorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-5,
-              out: torch.Tensor | None = None) -> torch.Tensor:
+              out: torch.Tensor | None = None, reverse: bool = False) -> torch.Tensor:
     _req(x, torch.bfloat16, "x"), _req(gamma, torch.float32, "gamma"), _req(beta, torch.float32, "beta")
     M, Cc = x.shape
     if out is None:
         out = torch.empty((M, Cc), device=x.device, dtype=torch.bfloat16)
     check(_lib.load().seva_layernorm(x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), gamma.data_ptr(),
-                                     beta.data_ptr(), M, Cc, eps, _stream()), "seva_layernorm")
+                                     beta.data_ptr(), M, Cc, eps, int(reverse), _stream()), "seva_layernorm")
     return out
 
 

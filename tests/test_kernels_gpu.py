@@ -418,3 +418,54 @@ def test_sampler_elementwise(ops):
     assert d4[..., 11:].abs().max() == 0 and d4[:, 0].abs().max() == 0
     back = ops.unpack_nchw(eps, N, 4, h, w)
     assert torch.equal(back, e)
+
+
+# ---------------------------------------------------------------------------------------------------
+def test_reverse_traversal_is_bit_identical(ops):
+    """`reverse` only changes the order in which tiles / rows are visited (L2-aware traversal): same bits."""
+    from seva_b200 import pack
+
+    g = torch.Generator(device="cuda").manual_seed(3)
+    rnd = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    # linear with bias + residual, geglu, conv3x3 with row bias; several tiles per CTA and ragged tails
+    A, W, b = bf(rnd(4097, 320)), bf(rnd(960, 320) / 18), rnd(960) * 0.1
+    res = bf(rnd(4097, 960))
+    for cl in (1, 2):
+        assert torch.equal(ops.linear(A, W, b, residual=res, cluster=cl),
+                           ops.linear(A, W, b, residual=res, cluster=cl, reverse=True))
+    Wg, bg = bf(rnd(2560, 320) / 18), rnd(2560) * 0.1
+    Wp, bp = pack.pack_geglu(Wg, bg, ops.pick_bn(2560, True))
+    assert torch.equal(ops.linear(A, Wp, bp, geglu=True), ops.linear(A, Wp, bp, geglu=True, reverse=True))
+    n_img, H, Cin, Cout = 3, 18, 128, 320
+    ximg = torch.zeros(n_img, H + 2, H + 2, Cin, device="cuda")
+    ximg[:, 1:-1, 1:-1] = rnd(n_img, H, H, Cin)
+    x = bf(ximg.reshape(-1, Cin))
+    W9 = pack.pack_conv3x3(bf(rnd(Cout, Cin, 3, 3) / 34))
+    rb = rnd(n_img, Cout)
+    assert torch.equal(ops.conv3x3_padded(x, W9, None, n_img, H, H, rowbias=rb),
+                       ops.conv3x3_padded(x, W9, None, n_img, H, H, rowbias=rb, reverse=True))
+    # norms
+    gamma, beta = rnd(320), rnd(320)
+    xn = bf(rnd(3 * 20 * 20, 320))
+    dmap, dw, db = rnd(3, 18 * 18, 6), rnd(640, 6) * 0.3, rnd(640) * 0.3
+    for dense in (False, True):
+        kw = dict(silu=True, dense=dmap if dense else None, dense_w=dw if dense else None, dense_b=db if dense else None)
+        assert torch.equal(ops.groupnorm(xn, gamma, beta, 3, 18, 18, **kw),
+                           ops.groupnorm(xn, gamma, beta, 3, 18, 18, reverse=True, **kw))
+    xl = bf(rnd(1001, 320))
+    assert torch.equal(ops.layernorm(xl, gamma, beta), ops.layernorm(xl, gamma, beta, reverse=True))
+
+
+def test_groupnorm_stats_buffer_reuse_is_deterministic(ops):
+    """The ticket counters reset themselves: reusing one stats buffer across launches gives identical totals."""
+    g = torch.Generator(device="cuda").manual_seed(4)
+    n_img, rpi, Cc = 5, 38 * 38, 640
+    x = bf(torch.randn(n_img * rpi, Cc, device="cuda", generator=g))
+    sums = torch.zeros(ops.gn_stats_floats(n_img, rpi, Cc), device="cuda")
+    outs = []
+    for rev in (False, True, False):
+        ops.groupnorm_stats(x, n_img, rpi, Cc, sums, reverse=rev)
+        outs.append(sums[: n_img * Cc * 2].clone())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    ref = torch.stack([x.float().view(n_img, rpi, Cc).sum(1), (x.float() ** 2).view(n_img, rpi, Cc).sum(1)], -1)
+    assert rel_l2(outs[0].view(n_img, Cc, 2), ref) < 1e-5

@@ -26,7 +26,7 @@ if which in ("all", "gn"):
         y = torch.empty_like(x)
         gamma = torch.ones(C, device=dev); beta = torch.zeros(C, device=dev)
         dmap = torch.randn(N, H * H, 6, device=dev); dw = torch.randn(2 * C, 6, device=dev); db = torch.randn(2 * C, device=dev)
-        sums = torch.empty(N, C, 2, device=dev)
+        sums = torch.zeros(ops.gn_stats_floats(N, (H + 2) * (H + 2), C), device=dev)
         t1 = timeit(lambda: ops.groupnorm_stats(x, N, (H + 2) * (H + 2), C, sums))
         p = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=C, y_ptr=y.data_ptr(), ldy=C, sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(), n_img=N, H=H, Wd=H, Cc=C, groups=32, eps=1e-5, in_padded=True, out_padded=True, silu=True, dense_ptr=dmap.data_ptr() if dense else None, dense_w_ptr=dw.data_ptr() if dense else None, dense_b_ptr=db.data_ptr() if dense else None)
         t2 = timeit(lambda: ops.run_gn_apply(p))
