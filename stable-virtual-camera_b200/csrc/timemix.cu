@@ -219,19 +219,22 @@ __device__ __forceinline__ uint32_t tm_off(int row, int chunk) {
   return (uint32_t)(row * 128 + ((chunk ^ (row & 7)) << 4));
 }
 
-__global__ void __launch_bounds__(kTmmWarps * 32, 4)
+// KT = number of 32-row blocks along the frame axis: KT = 1 serves T <= 32 (the T = 21 default), KT = 2 serves
+// T <= 64 (BASELINE configs[4]); query blocks are processed one after the other against all KT key blocks.
+template <int KT>
+__global__ void __launch_bounds__(kTmmWarps * 32, KT == 1 ? 4 : 2)
 timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __restrict__ kp,
                    const __nv_bfloat16* __restrict__ vp, __nv_bfloat16* __restrict__ out, int B, int Tq, int T,
                    int S, int Hh, long long ldq, long long ldkv, long long ldo, float scale_log2, long long total,
                    long long nwarps_total) {
   extern __shared__ __align__(128) uint8_t tm_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t qS = smem_u32(tm_smem) + warp * kTmmBytes;
-  const uint32_t kS = qS + 4096, vS = qS + 8192;
+  const uint32_t qS = smem_u32(tm_smem) + warp * (KT * kTmmBytes);
+  const uint32_t kS = qS + KT * 4096, vS = qS + 2 * KT * 4096;
   const int sub = lane >> 3, part = lane & 7;  // staging: 8 lanes x 16 B per row, 4 rows per instruction
   const int g = lane >> 2, q4 = lane & 3;      // fragment coordinates
   // rows >= T stay zero for the whole kernel (V rows meet P = 0 there: they must be finite)
-  for (int i = lane; i < kTmmBytes / 16; i += 32)
+  for (int i = lane; i < KT * kTmmBytes / 16; i += 32)
     asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(qS + i * 16), "r"(0u) : "memory");
   __syncwarp();
 
@@ -243,7 +246,7 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
     // ---- stage Q, K, V: two rounds of 16 rows, each with its 12 row loads issued before the stores
     __syncwarp();  // the previous item's output staging has been read
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
+    for (int half = 0; half < 2 * KT; ++half) {
       if (half * 16 < T || half * 16 < Tq) {
         uint4 lq[4], lk[4], lv[4];
 #pragma unroll
@@ -272,26 +275,30 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
     }
     __syncwarp();
 
-    // ---- S = Q K^T : [2 m-tiles][4 n-tiles] of 16x8
-    float sc[2][4][4];
+#pragma unroll
+    for (int qb = 0; qb < KT; ++qb) {
+    if (qb * 32 >= Tq) break;
+    const uint32_t qB = qS + qb * 4096;  // this block's 32 query rows (later: its 32 output rows)
+    // ---- S = Q K^T : [2 m-tiles][4 KT n-tiles] of 16x8
+    float sc[2][4 * KT][4];
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
+      for (int nt = 0; nt < 4 * KT; ++nt)
 #pragma unroll
         for (int i = 0; i < 4; ++i) sc[mt][nt][i] = 0.f;
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
-      uint32_t af[2][4], bf[2][4];
+      uint32_t af[2][4], bf[2 * KT][4];
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt) ldsm_x4(qS + tm_off(mt * 16 + (lane & 15), ks * 2 + (lane >> 4)), af[mt]);
+      for (int mt = 0; mt < 2; ++mt) ldsm_x4(qB + tm_off(mt * 16 + (lane & 15), ks * 2 + (lane >> 4)), af[mt]);
 #pragma unroll
-      for (int np = 0; np < 2; ++np)
+      for (int np = 0; np < 2 * KT; ++np)
         ldsm_x4(kS + tm_off(np * 16 + (lane & 7) + ((lane >> 4) << 3), ks * 2 + ((lane >> 3) & 1)), bf[np]);
 #pragma unroll
       for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) mma_bf16(sc[mt][nt], af[mt], bf[nt >> 1][(nt & 1) * 2], bf[nt >> 1][(nt & 1) * 2 + 1]);
+        for (int nt = 0; nt < 4 * KT; ++nt) mma_bf16(sc[mt][nt], af[mt], bf[nt >> 1][(nt & 1) * 2], bf[nt >> 1][(nt & 1) * 2 + 1]);
     }
     // ---- softmax over keys (columns); thread holds rows g, g+8 of each m-tile, columns nt*8 + 2*q4 + {0,1}
     float inv_l[2][2];
@@ -301,7 +308,7 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
       for (int hr = 0; hr < 2; ++hr) {
         float mx = -INFINITY;
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
+        for (int nt = 0; nt < 4 * KT; ++nt)
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int key = nt * 8 + 2 * q4 + e;
@@ -314,7 +321,7 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
         float l = 0.f;
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
+        for (int nt = 0; nt < 4 * KT; ++nt)
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const float pv = fast_exp2(sc[mt][nt][hr * 2 + e] - mx);
@@ -335,7 +342,7 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
 #pragma unroll
         for (int i = 0; i < 4; ++i) oc[mt][dt][i] = 0.f;
 #pragma unroll
-    for (int kk = 0; kk < 2; ++kk) {
+    for (int kk = 0; kk < 2 * KT; ++kk) {
       uint32_t pa[2][4];
 #pragma unroll
       for (int mt = 0; mt < 2; ++mt) {
@@ -355,7 +362,7 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
         }
       }
     }
-    // ---- normalise, stage O in the Q tile (all Q reads are done), coalesced 16-byte row stores
+    // ---- normalise, stage O in this block's Q rows (all their reads are done)
     __syncwarp();
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
@@ -364,12 +371,14 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
         const int r0 = mt * 16 + g;
         const uint32_t w0 = pack_bf16x2(oc[mt][dt][0] * inv_l[mt][0], oc[mt][dt][1] * inv_l[mt][0]);
         const uint32_t w1 = pack_bf16x2(oc[mt][dt][2] * inv_l[mt][1], oc[mt][dt][3] * inv_l[mt][1]);
-        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qS + tm_off(r0, dt) + q4 * 4), "r"(w0) : "memory");
-        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qS + tm_off(r0 + 8, dt) + q4 * 4), "r"(w1) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qB + tm_off(r0, dt) + q4 * 4), "r"(w0) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(qB + tm_off(r0 + 8, dt) + q4 * 4), "r"(w1) : "memory");
       }
+    }  // query blocks
+    // ---- coalesced 16-byte row stores of the staged outputs
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < 8; ++r) {
+    for (int r = 0; r < 8 * KT; ++r) {
       const int t = 4 * r + sub;
       if (t < Tq) {
         uint4 u;
@@ -391,20 +400,21 @@ struct TmArgs {
   float scale_log2;
 };
 
+template <int KT>
 int launch_timemix_mma(const TmArgs& a, cudaStream_t stream) {
-  const size_t smem = (size_t)kTmmWarps * kTmmBytes;
+  const size_t smem = (size_t)kTmmWarps * KT * kTmmBytes;
   static bool attr_set = false;
   if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(timemix_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SEVA_CUDA(cudaFuncSetAttribute(timemix_mma_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
   const long long total = (long long)a.B * a.S * a.Hh;
-  long long grid = 4ll * sm_count();  // 16 warps per SM, each striding over items
+  long long grid = (KT == 1 ? 4ll : 2ll) * sm_count();  // resident blocks per SM, each warp striding over items
   const long long need = (total + kTmmWarps - 1) / kTmmWarps;
   if (grid > need) grid = need;
-  timemix_mma_kernel<<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(a.q, a.k, a.v, a.out, a.B, a.Tq, a.Tk, a.S,
-                                                                       a.Hh, a.ldq, a.ldkv, a.ldo, a.scale_log2,
-                                                                       total, grid * kTmmWarps);
+  timemix_mma_kernel<KT><<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(a.q, a.k, a.v, a.out, a.B, a.Tq, a.Tk,
+                                                                           a.S, a.Hh, a.ldq, a.ldkv, a.ldo,
+                                                                           a.scale_log2, total, grid * kTmmWarps);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
@@ -428,8 +438,8 @@ int launch_timemix(const TmArgs& a, cudaStream_t stream) {
 }
 
 int timemix_dispatch(const TmArgs& a, cudaStream_t stream) {
-  if (a.Tk <= 32) return launch_timemix_mma(a, stream);
-  if (a.Tk <= 64) return launch_timemix<64>(a, stream);
+  if (a.Tk <= 32) return launch_timemix_mma<1>(a, stream);
+  if (a.Tk <= 64) return launch_timemix_mma<2>(a, stream);
   return launch_timemix<128>(a, stream);
 }
 

@@ -204,7 +204,8 @@ def test_attention_cross(ops, B, heads, Lq, Lk):
     assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
 
 
-@pytest.mark.parametrize("B,T,S,heads", [(2, 21, 81, 5), (1, 8, 324, 2), (2, 3, 50, 1), (1, 40, 30, 2)])
+@pytest.mark.parametrize("B,T,S,heads", [(2, 21, 81, 5), (1, 8, 324, 2), (2, 3, 50, 1), (1, 40, 30, 2), (1, 64, 20, 3),
+                                         (2, 33, 17, 1), (1, 32, 9, 2), (1, 70, 6, 1)])
 def test_timemix_attention(ops, B, T, S, heads):
     g = torch.Generator(device="cuda").manual_seed(T * S)
     Cc = heads * 64
