@@ -437,17 +437,22 @@ timestep_embedding_kernel(const long long* __restrict__ t, float* __restrict__ o
   if ((dim & 1) && k == 0) out[(long long)n * dim + dim - 1] = 0.f;
 }
 
-// out[m, n] = act(x[m, :]) . W[n, :] + bias[n]; 8 rows per block (x staged in smem), 64 columns per block.
+// out[m, n] = act(x[m, :]) . W[n, :] + bias[n].  A block owns 8 rows of x (staged in smem, fp32) and 128 output
+// columns, ONE COLUMN PER THREAD: the x values are warp-wide broadcast reads (one wavefront per LDS.128) and every
+// 16-byte weight load feeds 64 FMAs, so the kernel is FMA-bound.  (The first version gave each lane a k-slice of one
+// column: 2 LDS.128 with distinct addresses per 8 FMAs made it shared-memory bound, 450 us for the 22 time-embedding
+// projections at M = 42.)  A thread walks its own weight row; the eight 16-byte pieces of a 128-byte line are used by
+// consecutive iterations and hit in L1.
 // Grouped form: blockIdx.z selects one of `count` independent problems (descriptor table in device memory),
 // so the ~90 tiny per-step GEMVs (time-embedding projections, single-token cross-attention) are 3 launches.
 constexpr int kGemvRows = 8;
-constexpr int kGemvColsPerWarp = 8;
+constexpr int kGemvCols = 128;
 
 __device__ __forceinline__ void gemv_tile(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
                                           const float* __restrict__ bias, float* __restrict__ out, int M, int N,
                                           int K, int silu_in, int silu_out, float* xs) {
   const int m0 = blockIdx.y * kGemvRows;
-  if (m0 >= M || (int)blockIdx.x * (8 * kGemvColsPerWarp) >= N) return;
+  if (m0 >= M || (int)blockIdx.x * kGemvCols >= N) return;
   const int rows = min(kGemvRows, M - m0);
   const int K4 = K >> 2;
   const float4* x4 = reinterpret_cast<const float4*>(x + (long long)m0 * K);
@@ -467,48 +472,44 @@ __device__ __forceinline__ void gemv_tile(const float* __restrict__ x, const __n
     xs4[i] = v;
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll 1
-  for (int cc = 0; cc < kGemvColsPerWarp; ++cc) {
-    const int n = blockIdx.x * (8 * kGemvColsPerWarp) + warp * kGemvColsPerWarp + cc;
-    if (n >= N) break;
-    float acc[kGemvRows];
+  const int n = blockIdx.x * kGemvCols + threadIdx.x;
+  const bool active = n < N;
+  float acc[kGemvRows];
 #pragma unroll
-    for (int r = 0; r < kGemvRows; ++r) acc[r] = 0.f;
-    const __nv_bfloat16* wr = W + (long long)n * K;
-    for (int k = lane * 8; k < K; k += 256) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(wr + k));
-      const float wv[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
-                           bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
-#pragma unroll
-      for (int r = 0; r < kGemvRows; ++r) {
-        const float4 x0 = *reinterpret_cast<const float4*>(xs + r * K + k);
-        const float4 x1 = *reinterpret_cast<const float4*>(xs + r * K + k + 4);
-        acc[r] = fmaf(wv[0], x0.x, acc[r]);
-        acc[r] = fmaf(wv[1], x0.y, acc[r]);
-        acc[r] = fmaf(wv[2], x0.z, acc[r]);
-        acc[r] = fmaf(wv[3], x0.w, acc[r]);
-        acc[r] = fmaf(wv[4], x1.x, acc[r]);
-        acc[r] = fmaf(wv[5], x1.y, acc[r]);
-        acc[r] = fmaf(wv[6], x1.z, acc[r]);
-        acc[r] = fmaf(wv[7], x1.w, acc[r]);
-      }
-    }
+  for (int r = 0; r < kGemvRows; ++r) acc[r] = 0.f;
+  const uint4* wr = reinterpret_cast<const uint4*>(W + (long long)(active ? n : 0) * K);
+#pragma unroll 2
+  for (int k8 = 0; k8 < (K >> 3); ++k8) {
+    const uint4 u = __ldg(wr + k8);
+    const float wv[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
+                         bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
 #pragma unroll
     for (int r = 0; r < kGemvRows; ++r) {
-      float v = acc[r];
+      const float4 x0 = xs4[r * K4 + 2 * k8];
+      const float4 x1 = xs4[r * K4 + 2 * k8 + 1];
+      acc[r] = fmaf(wv[0], x0.x, acc[r]);
+      acc[r] = fmaf(wv[1], x0.y, acc[r]);
+      acc[r] = fmaf(wv[2], x0.z, acc[r]);
+      acc[r] = fmaf(wv[3], x0.w, acc[r]);
+      acc[r] = fmaf(wv[4], x1.x, acc[r]);
+      acc[r] = fmaf(wv[5], x1.y, acc[r]);
+      acc[r] = fmaf(wv[6], x1.z, acc[r]);
+      acc[r] = fmaf(wv[7], x1.w, acc[r]);
+    }
+  }
+  if (!active) return;
+  const float bv = bias != nullptr ? bias[n] : 0.f;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0 && r < rows) {
-        if (bias != nullptr) v += bias[n];
-        if (silu_out) v = v / (1.0f + __expf(-v));
-        out[(long long)(m0 + r) * N + n] = v;
-      }
+  for (int r = 0; r < kGemvRows; ++r) {
+    if (r < rows) {
+      float v = acc[r] + bv;
+      if (silu_out) v = v / (1.0f + __expf(-v));
+      out[(long long)(m0 + r) * N + n] = v;
     }
   }
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kGemvCols)
 gemv_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
                  const float* __restrict__ bias, float* __restrict__ out, int M, int N, int K, int silu_in,
                  int silu_out) {
@@ -516,7 +517,7 @@ gemv_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ 
   gemv_tile(x, W, bias, out, M, N, K, silu_in, silu_out, xs);
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kGemvCols)
 gemv_grouped_kernel(const SevaGemvProblem* __restrict__ probs) {
   extern __shared__ float xs[];
   const SevaGemvProblem p = probs[blockIdx.z];
@@ -729,8 +730,8 @@ extern "C" int seva_gemv_rows(const float* x, const void* W, const float* bias, 
                                    200 * 1024));
     smem_set = 200 * 1024;
   }
-  dim3 grid((N + 8 * kGemvColsPerWarp - 1) / (8 * kGemvColsPerWarp), (M + kGemvRows - 1) / kGemvRows);
-  gemv_rows_kernel<<<grid, 256, smem, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M,
+  dim3 grid((N + kGemvCols - 1) / kGemvCols, (M + kGemvRows - 1) / kGemvRows);
+  gemv_rows_kernel<<<grid, kGemvCols, smem, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M,
                                                 N, K, silu_in, silu_out);
   SEVA_CUDA(cudaGetLastError());
   return 0;
@@ -748,8 +749,8 @@ extern "C" int seva_gemv_grouped(const SevaGemvProblem* problems_dev, int32_t co
     SEVA_CUDA(cudaFuncSetAttribute(gemv_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     smem_set = 200 * 1024;
   }
-  dim3 grid((max_N + 8 * kGemvColsPerWarp - 1) / (8 * kGemvColsPerWarp), (max_M + kGemvRows - 1) / kGemvRows, count);
-  gemv_grouped_kernel<<<grid, 256, smem, stream>>>(problems_dev);
+  dim3 grid((max_N + kGemvCols - 1) / kGemvCols, (max_M + kGemvRows - 1) / kGemvRows, count);
+  gemv_grouped_kernel<<<grid, kGemvCols, smem, stream>>>(problems_dev);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

@@ -28,8 +28,11 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kGemmThreads = 320;
-constexpr int kEpiWarps = 8;
+#ifndef SEVA_EPI_WARPS
+#define SEVA_EPI_WARPS 8
+#endif
+constexpr int kEpiWarps = SEVA_EPI_WARPS;   // multiple of 4: every TMEM lane quarter is drained by kEpiWarps / 4 warps
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kSmemMax = 232448;         // 227 KB: the most dynamic smem one CTA can opt in to
 constexpr int kCtrlBytes = 1024;         // barriers + tmem pointer live in the first KB
 constexpr int kPatchBytes = 4096;        // per-epilogue-warp transpose patch: 32 rows x 128 B
@@ -358,14 +361,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------- epilogue (every CTA) ---------------------------------------
     const int ew = warp - 2;
     const int quarter = warp & 3;        // TMEM lane quarter this warp may access
-    const int half = ew >> 2;            // which half of the tile's columns
+    const int part = ew >> 2;            // which share of the tile's columns
+    constexpr int kParts = kEpiWarps / 4;
     const int row_in_tile = quarter * 32 + lane;
     const uint32_t patch = patch_base + ew * kPatchBytes;
     const uint32_t bslot = bias_base + ew * kBiasSlotBytes;
     // accumulator columns this warp drains: [seg_lo, seg_lo + seg_len), for GEGLU also the gate twin at + bn/2
     const int nunits = a.geglu ? a.bn / 64 : a.bn / 32;
-    const int u_begin = half == 0 ? 0 : (nunits + 1) / 2;
-    const int u_end = half == 0 ? (nunits + 1) / 2 : nunits;
+    const int u_begin = (nunits * part + kParts - 1) / kParts;
+    const int u_end = (nunits * (part + 1) + kParts - 1) / kParts;
     const int seg_lo = u_begin * 32, seg_len = (u_end - u_begin) * 32;
     const bool has_cb = a.fast && (a.bias != nullptr || a.rowbias != nullptr);
 

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libseva_b200.so")
+LIB_PATH = os.environ.get("SEVA_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libseva_b200.so")  # override: developer A/B builds
 
 c_void_p, c_int, c_i64, c_float = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
