@@ -125,6 +125,20 @@ class FrameShard:
     def T_local(self) -> int:
         return self.t1 - self.t0
 
+    def space_parts(self, S: int) -> list:
+        """Contiguous ranges of the S spatial positions, one per rank (time-mix all-to-all)."""
+        from .dist import partition_frames
+
+        return partition_frames(S, self.size)
+
+    def stage_flat(self, n_send: int, n_recv: int, dtype, device):
+        key = ("flat", n_send, n_recv, dtype, device)
+        st = self._stage.get(key)
+        if st is None:
+            st = (torch.empty(n_send, dtype=dtype, device=device), torch.empty(n_recv, dtype=dtype, device=device))
+            self._stage[key] = st
+        return st
+
     def local(self, x: torch.Tensor, B: int) -> torch.Tensor:
         """[B*T_total, ...] -> this rank's [B*T_local, ...] (contiguous copy)."""
         return x.reshape(B, self.T_total, *x.shape[1:])[:, self.t0:self.t1].reshape(B * self.T_local, *x.shape[1:]) \
@@ -171,6 +185,55 @@ class _FrameGather:
         return 0
 
 
+class _SpaceExchange:
+    """Plan entry (called like a C-ABI launch): all-to-all between the frame-sharded token layout
+    [B, T_local, S, C] and the space-sharded layout [B, T_total, S_local, C].
+
+    Time-mix attention needs all FRAMES of one spatial position, not all positions: instead of gathering K/V of
+    every frame on every rank (2C per token of the whole chunk, P ranks -> (P-1)/P * 2C * P * local tokens received),
+    the packed q|k|v of the local frames is transposed to "all frames of my slice of positions" (3C per local token
+    sent once) and the attention output (C per token) is transposed back: 4C against 2C*P per local token, i.e. 4x less
+    NVLink traffic at 8 ranks, and the unsharded ``seva_timemix_attn`` kernel runs unchanged on the slice."""
+    __name__ = "frame_space_a2a"
+
+    def __init__(self, shard: FrameShard, to_space: bool, src, dst, B: int, S: int):
+        self.shard, self.to_space, self.src, self.dst, self.B, self.S = shard, to_space, src, dst, B, S
+        self.sparts = shard.space_parts(S)
+
+    def _frame_sharded(self, t):   # per peer d: the rows of MY frames at peer d's positions
+        sh = self.shard
+        v = t.view(self.B, sh.T_local, self.S, t.shape[1])
+        return [v[:, :, a:b] for a, b in self.sparts]
+
+    def _space_sharded(self, t):   # per peer r: the rows of peer r's frames at MY positions
+        sh = self.shard
+        a, b = self.sparts[sh.rank]
+        v = t.view(self.B, sh.T_total, b - a, t.shape[1])
+        return [v[:, t0:t1] for t0, t1 in sh.parts]
+
+    def views_out(self):
+        return self._frame_sharded(self.src) if self.to_space else self._space_sharded(self.src)
+
+    def views_in(self):
+        return self._space_sharded(self.dst) if self.to_space else self._frame_sharded(self.dst)
+
+    def __call__(self, stream) -> int:
+        import torch.distributed as dist
+
+        outs, ins = self.views_out(), self.views_in()
+        send, recv = self.shard.stage_flat(self.src.numel(), self.dst.numel(), self.src.dtype, self.src.device)
+        o = 0
+        for v in outs:
+            send[o:o + v.numel()].view(v.shape).copy_(v)
+            o += v.numel()
+        dist.all_to_all_single(recv, send, [v.numel() for v in ins], [v.numel() for v in outs], group=self.shard.group)
+        o = 0
+        for v in ins:
+            v.copy_(recv[o:o + v.numel()].view(v.shape))
+            o += v.numel()
+        return 0
+
+
 # ----------------------------------------------------------------------------------------------------
 # plan
 # ----------------------------------------------------------------------------------------------------
@@ -200,6 +263,10 @@ class Engine:
         self.bufs: dict = {}
         self.n_launch = 0
         self.gemv_groups: dict = {}
+        # time-mix attention under a frame shard: all-to-all to a space-sharded layout (default) or K/V all-gather
+        # (measured at T=21: 8 ranks 26.4 vs 30.2 ms/step in favour of the all-to-all, 4 ranks a tie, 2 ranks 59.0 vs 56.7)
+        env = os.environ.get("SEVA_TIMEMIX_A2A")
+        self.tm_a2a = (shard is not None and shard.size > 4) if env is None else env != "0"
         self.walk: dict = {}    # storage -> direction (True = descending rows) of the last kernel that touched it
         self.zigzag = os.environ.get("SEVA_ZIGZAG", "0") == "1"  # measured: no gain at T=21
         self.timing_sink: list | None = None  # set by bench.py to collect per-launch CUDA events
@@ -251,7 +318,7 @@ class Engine:
         (2*MAC for Linear/conv on unpadded pixels, 4*B*H*Lq*Lk*D for attention, activation bytes for norms)."""
         self.calls.append((fn, args))
         self.meta.append((fn.__name__, tag, float(flops), float(nbytes)))
-        if not isinstance(fn, _FrameGather):  # collectives are NCCL's kernels, not ours
+        if not isinstance(fn, (_FrameGather, _SpaceExchange)):  # collectives are NCCL's kernels, not ours
             self.n_launch += 1
 
     # ---- op emitters (each appends exactly one kernel launch unless noted) ---------------------
@@ -552,7 +619,21 @@ class Engine:
         y1 = self.buf(f"tk_y1_{l}", rc, C_)
         self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin")
         self.ln(y1, w["t_n1"], a)
-        if sh is not None:
+        if sh is not None and self.tm_a2a and S >= sh.size:
+            sa, sb = sh.space_parts(S)[sh.rank]
+            S_me = sb - sa
+            self.gemm(a, w["t_attn1"]["wqkv"], qkv)
+            qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * C_)
+            o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, C_)
+            self.add(_SpaceExchange(sh, True, qkv, qkv_sp, B, S), nbytes=2.0 * (qkv.numel() + qkv_sp.numel()),
+                     tag=f"to_space rows{rc} C{3 * C_}")
+            self.add(self.lib.seva_timemix_attn, qkv_sp.data_ptr(), o_sp.data_ptr(), B, self.Tk, S_me, heads,
+                     qkv_sp.stride(0), o_sp.stride(0), 0.125, flops=4.0 * B * S_me * heads * self.Tk * self.Tk * 64,
+                     nbytes=2.0 * 4 * qkv_sp.shape[0] * C_, tag=f"timemix BS{B * S_me} H{heads} T{self.Tk}")
+            self.add(_SpaceExchange(sh, False, o_sp, o, B, S), nbytes=2.0 * (o_sp.numel() + o.numel()),
+                     tag=f"to_frames rows{rc} C{C_}")
+            self._touch_forward(qkv, o)
+        elif sh is not None:
             q, kvl, kvf = self._split_qkv(a, w["t_attn1"]["wqkv"], l, C_, S)
             self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
                      o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,

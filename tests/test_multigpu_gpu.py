@@ -45,10 +45,12 @@ def _net_inputs(P, B, T, h, w, seed=5):
     return x, t, y, dense
 
 
+@pytest.mark.parametrize("a2a", [True, False])
 @pytest.mark.parametrize("T,B,ranks", [(5, 2, 2), (7, 1, 3), (8, 2, 4)])
-def test_frame_shard_emulated_on_one_gpu(T, B, ranks):
+def test_frame_shard_emulated_on_one_gpu(T, B, ranks, a2a, monkeypatch):
+    monkeypatch.setenv("SEVA_TIMEMIX_A2A", "1" if a2a else "0")
     from seva_b200 import ops
-    from seva_b200.engine import Engine, FrameShard, _FrameGather, pack_weights
+    from seva_b200.engine import Engine, FrameShard, _FrameGather, _SpaceExchange, pack_weights
 
     h = w = 16
     P, model = _tiny_model(T)
@@ -65,10 +67,16 @@ def test_frame_shard_emulated_on_one_gpu(T, B, ranks):
         ops.pack_nchw(s.local(x.float(), B), e.net_in)
         e.bind(s.local(t, B), s.local(y, B), s.local(dense, B), ctx0=y[::T])
     stream = torch.cuda.current_stream().cuda_stream
-    n_gather = 0
+    n_gather = n_a2a = 0
     for i in range(len(engs[0].calls)):
         fns = [e.calls[i][0] for e in engs]
-        if isinstance(fns[0], _FrameGather):
+        if isinstance(fns[0], _SpaceExchange):   # all-to-all: rank d receives from rank r what r addressed to d
+            n_a2a += 1
+            assert all(isinstance(f, _SpaceExchange) and f.to_space == fns[0].to_space for f in fns)
+            for d, dst in enumerate(fns):
+                for r, src in enumerate(fns):
+                    dst.views_in()[r].copy_(src.views_out()[d])
+        elif isinstance(fns[0], _FrameGather):
             n_gather += 1
             assert all(isinstance(f, _FrameGather) for f in fns)
             rpf = fns[0].a[4]
@@ -83,7 +91,11 @@ def test_frame_shard_emulated_on_one_gpu(T, B, ranks):
             for e in engs:
                 fn, args = e.calls[i]
                 assert fn(*args, stream) == 0
-    assert n_gather == 16 + sum(1 for m in seva.modules() if getattr(m, "name", "") in P.unflatten_names)
+    n3d = sum(1 for m in seva.modules() if getattr(m, "name", "") in P.unflatten_names)
+    if a2a:   # time-mix sites: two transposes each (the S < ranks site, if any, falls back to the K/V gather)
+        assert n_a2a % 2 == 0 and n_a2a // 2 + (n_gather - n3d) == 16 and n_gather >= n3d
+    else:
+        assert n_a2a == 0 and n_gather == 16 + n3d
     for e, s in zip(engs, shards):
         loc = ops.unpack_nchw(e.eps, e.N, P.out_channels, h, w).view(B, s.T_local, -1)
         want = ref.reshape(B, T, -1)[:, s.t0:s.t1]
@@ -140,7 +152,12 @@ def _nccl_worker(rank, world, port, ret):
         out = {"single": _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()}
         # frame sequence-parallel over both ranks (3 + 2 frames)
         model.module.set_frame_group(dist.group.WORLD)
-        out["frames"] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()
+        os.environ["SEVA_TIMEMIX_A2A"] = "1"
+        out["frames"] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()      # time-mix by all-to-all
+        os.environ["SEVA_TIMEMIX_A2A"] = "0"
+        model.module.set_frame_group(dist.group.WORLD)                          # plans are rebuilt
+        out["frames_gather"] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()  # time-mix by K/V all-gather
+        os.environ.pop("SEVA_TIMEMIX_A2A")
         model.module.set_frame_group(None)
         # CFG split: uncond on rank 0, cond on rank 1
         groups = D.build_groups(D.Topology(world, rank, cfg=2, sp=1))
@@ -182,6 +199,7 @@ def test_two_gpu_partitions_match_one_gpu():
     assert rel_l2(res[1]["single"], single) < 1e-2, rel_l2(res[1]["single"], single)
     for r in range(2):
         assert rel_l2(res[r]["frames"], single) < 2e-2, rel_l2(res[r]["frames"], single)
+        assert rel_l2(res[r]["frames_gather"], single) < 2e-2, rel_l2(res[r]["frames_gather"], single)
         assert rel_l2(res[r]["cfg"], single) < 2e-2, rel_l2(res[r]["cfg"], single)
     # the gathered tensors are the same bits on every rank, so the replicated sampler state cannot drift apart
     assert torch.equal(res[0]["frames"], res[1]["frames"]) and torch.equal(res[0]["cfg"], res[1]["cfg"])
