@@ -352,7 +352,9 @@ class Engine:
         """GroupNorm: stats launch (+ memset inside) and apply launch."""
         H, Wd = self.HW[l]
         rpi = (H + 2) * (Wd + 2) if in_padded else H * Wd
-        sums = self.buf("gn_sums", ops.gn_stats_floats(self.N, rpi, C_), 1, F32)  # zero-initialised, self-resetting
+        # one buffer per (rows, channels): its ticket words sit at a shape-dependent offset and must stay zero between
+        # launches, so shapes never share a buffer (zero-initialised by ``buf``, self-resetting afterwards)
+        sums = self.buf(f"gn_sums_{rpi}_{C_}", ops.gn_stats_floats(self.N, rpi, C_), 1, F32)
         act = 2.0 * self.N * H * Wd * C_
         self.add(self.lib.seva_groupnorm_stats, x.data_ptr(), x.stride(0), self.N, rpi, C_, sums.data_ptr(),
                  int(self._dir(x)), nbytes=act, tag=f"gn_stats HW{H * Wd} C{C_}")
