@@ -179,3 +179,21 @@ def test_config1_full_model_one_step_vs_reference():
     print(f"config1: denoiser rel-L2 {e_den:.3e}, x1 rel-L2 {e_x:.3e}")
     assert e_den < NET_TOL, e_den
     assert e_x < NET_TOL, e_x
+
+
+def test_tiny_50_steps_final_latents_vs_oracle(tiny):
+    """north_star: final latents within rel-L2 5e-2 of the fp32 reference after the full 50-step schedule (tiny network
+    here; tools/parity_50step.py runs the same check at BASELINE configs[1] size against the oracle on the GPU)."""
+    from seva_b200 import sampling as S
+
+    P, model, sd, g, _ = tiny
+    T, h, w, steps = 3, 16, 16, 50
+    inp = synth.make_inputs(T, 1, h, w, lambda *a: g["plucker"], seed=2, num_steps=steps, ctx_dim=P.context_dim)
+    x, cap = _sample_ours(model, inp, T, steps, 2.0, S.MultiviewCFG(1.2))
+    table = O.denoiser_table()
+    fs = O.multiview_scale(2.0, 1.2, inp["c2w"], inp["K"], inp["mask"])
+    with torch.inference_mode():
+        ref = O.sample(lambda xx, idx, c: O.sgm_forward(sd, P, xx, idx, c, num_frames=T), table, inp["x0"], fs,
+                       inp["c"], inp["uc"], steps, inp["eps"])
+    assert len(cap) == steps
+    assert rel_l2(x, ref) < 5e-2, rel_l2(x, ref)
