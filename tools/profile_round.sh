@@ -3,6 +3,7 @@
 # by the identical plain command exiting 0.  Outputs under gpurun_out/prof_$TAG/.
 #   gpurun --timeout 1500 -- 'bash tools/profile_round.sh r1b'
 TAG=${1:-r1}
+MODE=${2:-all}   # all | list (launch list only)
 OUT=gpurun_out/prof_$TAG
 mkdir -p $OUT
 BENCH="python bench.py --steps 1 --warmup 3 --no-cpu"
@@ -10,6 +11,7 @@ BENCH="python bench.py --steps 1 --warmup 3 --no-cpu"
 $BENCH > $OUT/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
     --log-file $OUT/launches.csv $BENCH > $OUT/ncu_bench.log 2>&1
+[ "$MODE" = list ] && { ls -la $OUT; exit 0; }
 # (2) --set full on the dominant shapes, each timed alone by the microbench tools (2 launches each)
 full() {  # name, kernel regex, skip, count, command...
   local name=$1 rx=$2 skip=$3 cnt=$4; shift 4
