@@ -157,11 +157,13 @@ gn_apply_kernel(const GNApplyArgs a) {
   const int Wp = a.W + 2;
   const long long rpi_pad = (long long)(a.H + 2) * Wp;
   for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
-    const float* sp = a.sums + ((long long)n * a.C + g * cpg) * 2;
+    const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
     float s = 0.f, q = 0.f;
-    for (int c = 0; c < cpg; ++c) {
-      s += sp[2 * c];
-      q += sp[2 * c + 1];
+#pragma unroll 8
+    for (int c = 0; c < cpg; ++c) {  // 8 independent loads in flight: this runs on 32 threads before anything else
+      const float2 v = __ldcg(sp + c);
+      s += v.x;
+      q += v.y;
     }
     const float cnt = (float)cpg * (float)HW;
     const float mean = s / cnt;
@@ -310,11 +312,13 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
   const int Wp = a.W + 2;
   const long long rpi_pad = (long long)(a.H + 2) * Wp;
   for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
-    const float* sp = a.sums + ((long long)n * a.C + g * cpg) * 2;
+    const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
     float s = 0.f, q = 0.f;
-    for (int c = 0; c < cpg; ++c) {
-      s += sp[2 * c];
-      q += sp[2 * c + 1];
+#pragma unroll 8
+    for (int c = 0; c < cpg; ++c) {  // 8 independent loads in flight: this runs on 32 threads before anything else
+      const float2 v = __ldcg(sp + c);
+      s += v.x;
+      q += v.y;
     }
     const float cnt = (float)cpg * (float)HW;
     const float mean = s / cnt;
@@ -347,13 +351,28 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
     sa[i] = f2(ta[0], ta[1]);
     sb[i] = f2(tb[0], tb[1]);
     const int c = c0 + 2 * i;
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      ws[i][k] = f2(a.dense_w[(long long)c * 6 + k], a.dense_w[(long long)(c + 1) * 6 + k]);
-      wh[i][k] = f2(a.dense_w[(long long)(a.C + c) * 6 + k], a.dense_w[(long long)(a.C + c + 1) * 6 + k]);
-    }
     bs[i] = f2(1.0f + a.dense_b[c], 1.0f + a.dense_b[c + 1]);  // fold the "1 +" of h*(1+scale)
     bh[i] = f2(a.dense_b[a.C + c], a.dense_b[a.C + c + 1]);
+  }
+  {
+    // the thread's 4 scale rows and 4 shift rows of dense_w [2C, 6] are 24 contiguous floats each: 12 16-byte loads
+    // (48 scalar loads per thread made the per-block set-up ~15 us, a third of the kernel at two waves per SM)
+    float wr[24], hr[24];
+    const float4* ps = reinterpret_cast<const float4*>(a.dense_w + (long long)c0 * 6);
+    const float4* ph = reinterpret_cast<const float4*>(a.dense_w + (long long)(a.C + c0) * 6);
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      const float4 u = __ldg(ps + j), v = __ldg(ph + j);
+      wr[4 * j] = u.x; wr[4 * j + 1] = u.y; wr[4 * j + 2] = u.z; wr[4 * j + 3] = u.w;
+      hr[4 * j] = v.x; hr[4 * j + 1] = v.y; hr[4 * j + 2] = v.z; hr[4 * j + 3] = v.w;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        ws[i][k] = f2(wr[(2 * i) * 6 + k], wr[(2 * i + 1) * 6 + k]);
+        wh[i][k] = f2(hr[(2 * i) * 6 + k], hr[(2 * i + 1) * 6 + k]);
+      }
   }
 
   const int p_begin = bx * a.pix_per_block;
@@ -403,18 +422,14 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
   load_dense(dptr, p0, dA);
   load_dense(dptr + dstep, p0 + PPB, dB);
   dptr += 2 * dstep;
-  // one pixel: consume the ring slot and the Plucker buffer `d`, then refill both (slot: kGnRing pixels ahead;
-  // d: two pixels ahead -- the loop is unrolled by two so that dA / dB alternate without register moves)
-  auto pixel = [&](float2 (&d)[3]) {
-    asm volatile("cp.async.wait_group %0;" ::"n"(kGnRing - 1) : "memory");
-    uint32_t w0, w1;
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(w0), "=r"(w1) : "r"(ring + slot * ring_pitch) : "memory");
-    prefetch(slot);  // refill the slot just consumed
-    slot = slot + 1 == kGnRing ? 0 : slot + 1;
+  // Two pixels per trip: both ring slots are read, both refills issued, then the arithmetic of the two pixels (8
+  // independent FFMA2 chains) runs without an asm barrier in between, then the Plucker buffers are refilled (two
+  // pixels ahead each) and the rows stored.
+  auto compute = [&](uint32_t w0, uint32_t w1, const float2 (&d)[3], uint32_t (&o)[2]) {
     f2_t pk[6];
     pk[0] = f2(d[0].x, d[0].x); pk[1] = f2(d[0].y, d[0].y); pk[2] = f2(d[1].x, d[1].x);
     pk[3] = f2(d[1].y, d[1].y); pk[4] = f2(d[2].x, d[2].x); pk[5] = f2(d[2].y, d[2].y);
-    uint32_t wv[2] = {w0, w1};
+    const uint32_t wv[2] = {w0, w1};
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
       f2_t h = f2fma(f2(bf16_lo(wv[i]), bf16_hi(wv[i])), sa[i], sb[i]);
@@ -430,17 +445,31 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
         sh = f2fma(wh[i][k], pk[k], sh);
       }
       h = f2fma(h, sc, sh);
-      wv[i] = pack_bf16x2(f2lo(h), f2hi(h));
+      o[i] = pack_bf16x2(f2lo(h), f2hi(h));
     }
-    load_dense(dptr, cur.p + 2 * PPB, d);   // after the last use of d
-    dptr += dstep;
-    *reinterpret_cast<uint2*>(a.y + cur.off) = make_uint2(wv[0], wv[1]);
-    advance(cur, step_out_q, wrap_out);
   };
   while (cur.p < p_end) {
-    pixel(dA);
-    if (cur.p >= p_end) break;
-    pixel(dB);
+    const bool two = cur.p + PPB < p_end;
+    asm volatile("cp.async.wait_group %0;" ::"n"(kGnRing - 2) : "memory");
+    const int slot_b = slot + 1 == kGnRing ? 0 : slot + 1;
+    uint32_t a0, a1, b0, b1;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(a0), "=r"(a1) : "r"(ring + slot * ring_pitch) : "memory");
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(ring + slot_b * ring_pitch) : "memory");
+    prefetch(slot);    // refill the two slots just consumed
+    prefetch(slot_b);
+    slot = slot_b + 1 == kGnRing ? 0 : slot_b + 1;
+    uint32_t oa[2], ob[2];
+    compute(a0, a1, dA, oa);
+    compute(b0, b1, dB, ob);
+    load_dense(dptr, cur.p + 2 * PPB, dA);
+    load_dense(dptr + dstep, cur.p + 3 * PPB, dB);
+    dptr += 2 * dstep;
+    *reinterpret_cast<uint2*>(a.y + cur.off) = make_uint2(oa[0], oa[1]);
+    advance(cur, step_out_q, wrap_out);
+    if (two) {
+      *reinterpret_cast<uint2*>(a.y + cur.off) = make_uint2(ob[0], ob[1]);
+      advance(cur, step_out_q, wrap_out);
+    }
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 
@@ -590,6 +619,7 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
              "seva_groupnorm_apply: bad C=%d groups=%d", p->C, p->groups);
   SEVA_CHECK((p->ldx % 4) == 0 && (p->ldy % 4) == 0, "seva_groupnorm_apply: ldx/ldy must be multiples of 4");
   SEVA_CHECK(!p->dense || (p->dense_w && p->dense_b), "seva_groupnorm_apply: dense needs dense_w/dense_b");
+  SEVA_CHECK(!p->dense || ((uintptr_t)p->dense_w & 15) == 0, "seva_groupnorm_apply: dense_w must be 16-byte aligned");
   GNApplyArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(p->x);
   a.ldx = p->ldx;
