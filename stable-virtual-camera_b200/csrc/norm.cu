@@ -311,6 +311,20 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
   const int HW = a.H * a.W;
   const int Wp = a.W + 2;
   const long long rpi_pad = (long long)(a.H + 2) * Wp;
+  // The block's whole slice of the Plucker map (pix_per_block x 6 fp32, ~18 KB) is copied to shared memory up front and
+  // read back with broadcast loads: as per-thread global loads one trip ahead, 18 % of the stall samples sat on their
+  // first use (ncu r1e; the streaming row copies evict them from L1).  Its latency overlaps the group-stat loads below.
+  const int p_begin = bx * a.pix_per_block;
+  const int p_end = min(HW, p_begin + a.pix_per_block);
+  const uint32_t ring_base = smem_u32(gstat) + ((2 * a.groups * 4 + 15) & ~15);
+  const uint32_t slab = ring_base + kGnRing * blockDim.x * 8;
+  {
+    const char* src = reinterpret_cast<const char*>(a.dense + ((long long)n * HW + p_begin) * 6);
+    const int n8 = (p_end - p_begin) * 3;
+    for (int i = threadIdx.x; i < n8; i += blockDim.x)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(slab + i * 8), "l"(src + i * 8) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
   for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
     const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
     float s = 0.f, q = 0.f;
@@ -326,8 +340,7 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
     gstat[2 * g] = mean;
     gstat[2 * g + 1] = rsqrtf(var + a.eps);
   }
-  __syncthreads();
-  const uint32_t ring = smem_u32(gstat) + ((2 * a.groups * 4 + 15) & ~15) + threadIdx.x * 8;
+  const uint32_t ring = ring_base + threadIdx.x * 8;
   const uint32_t ring_pitch = blockDim.x * 8;
 
   const int CG = a.cslice / 4;
@@ -336,24 +349,6 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
   const int PPB = blockDim.x / CG;
   const int c0 = blockIdx.z * a.cslice + cg * 4;
   f2_t sa[2], sb[2], ws[2][6], wh[2][6], bs[2], bh[2];
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    float ta[2], tb[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int c = c0 + 2 * i + e;
-      const int g = c / cpg;
-      const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
-      const float ga = a.gamma[c], be = a.beta[c];
-      ta[e] = rstd * ga;
-      tb[e] = fmaf(-mean, rstd * ga, be);
-    }
-    sa[i] = f2(ta[0], ta[1]);
-    sb[i] = f2(tb[0], tb[1]);
-    const int c = c0 + 2 * i;
-    bs[i] = f2(1.0f + a.dense_b[c], 1.0f + a.dense_b[c + 1]);  // fold the "1 +" of h*(1+scale)
-    bh[i] = f2(a.dense_b[a.C + c], a.dense_b[a.C + c + 1]);
-  }
   {
     // the thread's 4 scale rows and 4 shift rows of dense_w [2C, 6] are 24 contiguous floats each: 12 16-byte loads
     // (48 scalar loads per thread made the per-block set-up ~15 us, a third of the kernel at two waves per SM)
@@ -374,9 +369,27 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
         wh[i][k] = f2(hr[(2 * i) * 6 + k], hr[(2 * i + 1) * 6 + k]);
       }
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();  // group statistics and the Plucker slab are visible to the block
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    float ta[2], tb[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * i + e;
+      const int g = c / cpg;
+      const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
+      const float ga = a.gamma[c], be = a.beta[c];
+      ta[e] = rstd * ga;
+      tb[e] = fmaf(-mean, rstd * ga, be);
+    }
+    sa[i] = f2(ta[0], ta[1]);
+    sb[i] = f2(tb[0], tb[1]);
+    const int c = c0 + 2 * i;
+    bs[i] = f2(1.0f + a.dense_b[c], 1.0f + a.dense_b[c + 1]);  // fold the "1 +" of h*(1+scale)
+    bh[i] = f2(a.dense_b[a.C + c], a.dense_b[a.C + c + 1]);
+  }
 
-  const int p_begin = bx * a.pix_per_block;
-  const int p_end = min(HW, p_begin + a.pix_per_block);
   const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
   const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
   const f2_t half2 = f2(0.5f, 0.5f);
@@ -412,19 +425,15 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
 #pragma unroll
   for (int d = 0; d < kGnRing; ++d) prefetch(d);
   int slot = 0;
-  // the 6 Plucker values of a pixel are fetched two pixels ahead (L1/L2 hits, but ~300 cycles when exposed)
-  const float2* dptr = reinterpret_cast<const float2*>(a.dense + ((long long)n * HW + p0) * 6);
-  const int dstep = PPB * 3;  // float2 units per step
-  auto load_dense = [&](const float2* dp, int p, float2 (&d)[3]) {
-    if (p < p_end) { d[0] = __ldg(dp); d[1] = __ldg(dp + 1); d[2] = __ldg(dp + 2); }
+  uint32_t dsl = slab + pl * 24;  // this thread's pixel in the Plucker slab
+  const uint32_t dsl_step = PPB * 24;
+  auto load_dense = [&](uint32_t addr, float2 (&d)[3]) {
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+      asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(d[q].x), "=f"(d[q].y) : "r"(addr + q * 8) : "memory");
   };
-  float2 dA[3], dB[3];
-  load_dense(dptr, p0, dA);
-  load_dense(dptr + dstep, p0 + PPB, dB);
-  dptr += 2 * dstep;
   // Two pixels per trip: both ring slots are read, both refills issued, then the arithmetic of the two pixels (8
-  // independent FFMA2 chains) runs without an asm barrier in between, then the Plucker buffers are refilled (two
-  // pixels ahead each) and the rows stored.
+  // independent FFMA2 chains) runs without an asm barrier in between, then the rows are stored.
   auto compute = [&](uint32_t w0, uint32_t w1, const float2 (&d)[3], uint32_t (&o)[2]) {
     f2_t pk[6];
     pk[0] = f2(d[0].x, d[0].x); pk[1] = f2(d[0].y, d[0].y); pk[2] = f2(d[1].x, d[1].x);
@@ -458,12 +467,13 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
     prefetch(slot);    // refill the two slots just consumed
     prefetch(slot_b);
     slot = slot_b + 1 == kGnRing ? 0 : slot_b + 1;
+    float2 dA[3], dB[3];
+    load_dense(dsl, dA);
+    if (two) load_dense(dsl + dsl_step, dB);
+    dsl += 2 * dsl_step;
     uint32_t oa[2], ob[2];
     compute(a0, a1, dA, oa);
     compute(b0, b1, dB, ob);
-    load_dense(dptr, cur.p + 2 * PPB, dA);
-    load_dense(dptr + dstep, cur.p + 3 * PPB, dB);
-    dptr += 2 * dstep;
     *reinterpret_cast<uint2*>(a.y + cur.off) = make_uint2(oa[0], oa[1]);
     advance(cur, step_out_q, wrap_out);
     if (two) {
@@ -620,6 +630,7 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   SEVA_CHECK((p->ldx % 4) == 0 && (p->ldy % 4) == 0, "seva_groupnorm_apply: ldx/ldy must be multiples of 4");
   SEVA_CHECK(!p->dense || (p->dense_w && p->dense_b), "seva_groupnorm_apply: dense needs dense_w/dense_b");
   SEVA_CHECK(!p->dense || ((uintptr_t)p->dense_w & 15) == 0, "seva_groupnorm_apply: dense_w must be 16-byte aligned");
+  SEVA_CHECK(!p->dense || ((uintptr_t)p->dense & 7) == 0, "seva_groupnorm_apply: dense must be 8-byte aligned");
   GNApplyArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(p->x);
   a.ldx = p->ldx;
@@ -669,12 +680,14 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
     long long max_gx = HW / (2ll * ppb * unroll);
     if (max_gx < 1) max_gx = 1;
     if (max_gx > 64) max_gx = 64;
-    long long best_gx = 1;
+    const long long min_gx = p->dense ? (HW + 4095) / 4096 : 1;  // dense: the block's Plucker slab stays under 96 KB
+    if (max_gx < min_gx) max_gx = min_gx;
+    long long best_gx = min_gx;
     double best_eff = -1.0;
-    for (long long gx = 1; gx <= max_gx; ++gx) {
+    for (long long gx = min_gx; gx <= max_gx; ++gx) {
       const long long total = gx * per_img;
       const long long waves = (total + slots - 1) / slots;
-      if (waves > 4) break;
+      if (waves > 4 && gx > min_gx) break;
       const double eff = (double)total / (double)(waves * slots);
       if (eff >= best_eff - 1e-9) { best_eff = eff; best_gx = gx; }
     }
@@ -683,10 +696,11 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   dim3 grid((HW + a.pix_per_block - 1) / a.pix_per_block, p->Nimg, nslice);
   const size_t smem = sizeof(float) * 2 * p->groups;
   if (p->dense) {
-    const size_t smem_d = ((smem + 15) & ~(size_t)15) + (size_t)kGnRing * threads * 8;
+    const size_t smem_d = ((smem + 15) & ~(size_t)15) + (size_t)kGnRing * threads * 8 + (size_t)a.pix_per_block * 24;
+    SEVA_CHECK(smem_d <= 200 * 1024, "seva_groupnorm_apply: Plucker slab of %d pixels does not fit", a.pix_per_block);
     static bool attr_set = false;
     if (!attr_set) {
-      SEVA_CUDA(cudaFuncSetAttribute(gn_apply_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      SEVA_CUDA(cudaFuncSetAttribute(gn_apply_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
       attr_set = true;
     }
     gn_apply_dense_kernel<<<grid, threads, smem_d, stream>>>(a);
