@@ -294,7 +294,7 @@ def run_ours(args):
                    "l2": "activations per step (>2 GB) exceed the 126 MB L2; no explicit flush"},
         "e2e": {"value": round(e2e_v, 3), "unit": "frame-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e / steps, 3)},
-        "gpu_launches": eng.n_launch * steps + 4 * steps,
+        "gpu_launches": eng.n_launch_step * steps + 4 * steps,
         "clocks": clk, "roofline": roof, "ms_per_step_with_launch_events": round(ms_inst / steps, 3),
         "step_tflops": round(chunks_world * tf_step * steps / (ms_dev / 1e3), 1) if tf_step else None,
         "step_frac_of_peak": round(chunks_world * tf_step * steps / (ms_dev / 1e3) / peaks["tf_sustained"] / world, 4)

@@ -196,8 +196,14 @@ class CFGSplit(object):
         return getattr(self.__dict__["guider"], name)
 
     def prepare_inputs(self, x: torch.Tensor, s: torch.Tensor, c: dict, uc: dict):
+        from .sampling import COND_EPOCH, _EPOCHS, _same_cond, _version
+
         pick = uc if self.half == 0 else c
-        c_out = dict()
+        ident = [(k, pick[k], pick[k], _version(pick[k]), 0) for k in c if k in _CAT_KEYS]
+        cache = self.__dict__.get("_cond_cache")
+        if cache is None or not _same_cond(cache[0], ident):  # one conditioning epoch per (half, loop), as VanillaCFG
+            cache = self.__dict__["_cond_cache"] = (ident, next(_EPOCHS))
+        c_out = {COND_EPOCH: cache[1]}
         for k in c:
             if k in _CAT_KEYS:
                 c_out[k] = pick[k]
@@ -205,6 +211,12 @@ class CFGSplit(object):
                 assert c[k] == uc[k]
                 c_out[k] = c[k]
         return x, s, c_out
+
+    def reset_cache(self) -> None:
+        self.__dict__.pop("_cond_cache", None)
+        reset = getattr(self.guider, "reset_cache", None)
+        if reset is not None:
+            reset()
 
     def gather(self, denoised: torch.Tensor) -> torch.Tensor:
         out = torch.empty((2 * denoised.shape[0],) + tuple(denoised.shape[1:]), dtype=denoised.dtype,

@@ -270,6 +270,11 @@ class Engine:
         self.walk: dict = {}    # storage -> direction (True = descending rows) of the last kernel that touched it
         self.zigzag = os.environ.get("SEVA_ZIGZAG", "0") == "1"  # measured: no gain at T=21
         self.timing_sink: list | None = None  # set by bench.py to collect per-launch CUDA events
+        # Step-invariant hoisting: launches that read only the conditioning (Plucker resizes, Lk = 1
+        # cross-attention vectors) are skipped while ``bind`` is handed the same conditioning epoch as last time.
+        self._invariant: set = set()
+        self._epoch = None
+        self._skip_invariant = False
 
         # static inputs
         self.net_in = self.buf("net_in", self.rows_p(0), 64)
@@ -403,6 +408,9 @@ class Engine:
             self.calls.insert(pos, (self.lib.seva_gemv_grouped, args))
             self.meta.insert(pos, ("seva_gemv_grouped", name, 0.0, 0.0))
             self.n_launch += 1
+            self._invariant = {i + 1 if i >= pos else i for i in self._invariant}
+            if name != "emb":  # the cross-attention vectors depend on the context only, not on the step
+                self._invariant.add(pos)
             pos += 1
 
     # ---- network -------------------------------------------------------------------------------
@@ -422,6 +430,7 @@ class Engine:
         self.dense = []
         for l, (H, Wd) in enumerate(self.HW):
             d = self.buf(f"dense{l}", N, H * Wd * p.dense_in_channels, F32)
+            self._invariant.add(len(self.calls))  # depends on the Plucker map only
             self.add(lib.seva_resize_bilinear_ac, self.dense_in.data_ptr(), d.data_ptr(), N, p.dense_in_channels,
                      self.h, self.w, H, Wd)
             self.dense.append(d)
@@ -695,27 +704,49 @@ class Engine:
         self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin)
 
     # ---- execution ------------------------------------------------------------------------------
-    def bind(self, t: torch.Tensor, ctx: torch.Tensor, dense: torch.Tensor, ctx0: torch.Tensor | None = None) -> None:
+    def cond_current(self, epoch) -> bool:
+        """True if the conditioning of ``epoch`` is already bound (the caller can skip preparing it)."""
+        return epoch is not None and epoch == self._epoch
+
+    def bind(self, t: torch.Tensor, ctx: torch.Tensor | None, dense: torch.Tensor | None,
+             ctx0: torch.Tensor | None = None, epoch=None) -> None:
         """Copy the per-call conditioning into the plan's static input buffers (device-to-device).  ``ctx0`` is
         ``context[::T]`` (transformer.py:222-229); a frame shard passes the full batch's, since frame 0 may live
-        on another rank."""
+        on another rank.  ``epoch`` (from the guider's ``prepare_inputs`` cache, one value per sampling loop and
+        conditioning) marks ctx / dense as unchanged since the last call with the same value: they are not copied
+        again and the launches that depend only on them are skipped by ``run``."""
         self.t_in.copy_(t.reshape(-1))
+        if self.cond_current(epoch):
+            self._skip_invariant = True
+            return
         self.ctx_in.copy_(ctx)
         self.ctx0_in.copy_(ctx[:: self.T] if ctx0 is None else ctx0)
         self.dense_in.copy_(dense)
+        self._epoch = epoch
+        self._skip_invariant = False
+
+    @property
+    def n_launch_step(self) -> int:
+        """Launches of a step whose conditioning is already bound."""
+        return self.n_launch - len(self._invariant)
 
     def run(self, timing: list | None = None) -> None:
         """Launch the plan on the current stream.  With ``timing`` (a list), a CUDA-event pair is recorded around
         every launch and (index, start, end) is appended; read ``self.meta[index]`` for name / algorithmic work."""
         stream = torch.cuda.current_stream().cuda_stream
         timing = self.timing_sink if timing is None else timing
+        skip = self._invariant if self._skip_invariant else ()
         if timing is None:
-            for fn, args in self.calls:
+            for i, (fn, args) in enumerate(self.calls):
+                if i in skip:
+                    continue
                 rc = fn(*args, stream)
                 if rc != 0:
                     raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
             return
         for i, (fn, args) in enumerate(self.calls):
+            if i in skip:
+                continue
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             rc = fn(*args, stream)

@@ -255,7 +255,9 @@ class Seva(nn.Module):
         return eng
 
     def forward(self, x: torch.Tensor, t: torch.Tensor, y: torch.Tensor, dense_y: torch.Tensor,
-                num_frames: int | None = None) -> torch.Tensor:
+                num_frames: int | None = None, cond_epoch=None) -> torch.Tensor:
+        """``cond_epoch`` (optional, from the guider's prepared conditioning): y / dense_y are unchanged since the
+        last call with the same value, so the plan skips its conditioning-only launches."""
         num_frames = num_frames or self.params.num_frames
         if not x.is_cuda:
             raise SevaB200Error("Seva.forward needs CUDA tensors (seva_b200 has no CPU fallback)")
@@ -267,13 +269,17 @@ class Seva(nn.Module):
             sh = eng.shard
             if sh is None:
                 ops.pack_nchw(x.float(), eng.net_in)
-                eng.bind(t, y, dense_y)
+                eng.bind(t, y, dense_y, epoch=cond_epoch)
                 eng.run()
                 out = ops.unpack_nchw(eng.eps, n, self.params.out_channels, h, w)
             else:  # this rank's frames in, every rank's frames out
                 B = n // num_frames
                 ops.pack_nchw(sh.local(x.float(), B), eng.net_in)
-                eng.bind(sh.local(t, B), sh.local(y.float(), B), sh.local(dense_y.float(), B), ctx0=y[::num_frames])
+                if eng.cond_current(cond_epoch):
+                    eng.bind(sh.local(t, B), None, None, epoch=cond_epoch)
+                else:
+                    eng.bind(sh.local(t, B), sh.local(y.float(), B), sh.local(dense_y.float(), B), ctx0=y[::num_frames],
+                             epoch=cond_epoch)
                 eng.run()
                 loc = ops.unpack_nchw(eng.eps, eng.N, self.params.out_channels, h, w)
                 out = torch.empty((n,) + tuple(loc.shape[1:]), device=loc.device, dtype=loc.dtype)
@@ -290,4 +296,6 @@ class SGMWrapper(nn.Module):
         concat = c.get("concat", None)
         if concat is not None and concat.numel() > 0:
             x = torch.cat((x, concat.type_as(x)), dim=1)
+        if isinstance(self.module, Seva) and c.get("_cond_epoch") is not None:
+            kwargs = dict(kwargs, cond_epoch=c["_cond_epoch"])
         return self.module(x, t=t, y=c["crossattn"], dense_y=c["dense_vector"], **kwargs)

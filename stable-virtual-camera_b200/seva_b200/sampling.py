@@ -10,6 +10,8 @@ as the reference builds them, so sigma indices are bit-exact.
 """
 from __future__ import annotations
 
+import itertools
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -141,7 +143,7 @@ class DiscreteDenoiser(object):
             blended = torch.empty((n, 4, h, w), device=input.device, dtype=torch.float32)
             ops.denoise_prepare(input.float().contiguous(), None if replace is None else replace.float().contiguous(),
                                 cond["concat"].float().contiguous(), c_in, eng.net_in, blended, n, n, h, w)
-            eng.bind(idx, cond["crossattn"], cond["dense_vector"])
+            eng.bind(idx, cond["crossattn"], cond["dense_vector"], epoch=cond.get(COND_EPOCH))
             eng.run()
             out = torch.empty_like(blended)
             ops.denoise_finish(eng.eps, blended, c_out, out, n, h, w)
@@ -156,8 +158,12 @@ class DiscreteDenoiser(object):
         blended = torch.empty((nl, 4, h, w), device=input.device, dtype=torch.float32)
         ops.denoise_prepare(loc(input), None if replace is None else loc(replace), loc(cond["concat"]), loc(c_in),
                             eng.net_in, blended, nl, nl, h, w)
-        ctx = cond["crossattn"].float()
-        eng.bind(sh.local(idx, B), sh.local(ctx, B), loc(cond["dense_vector"]), ctx0=ctx[::num_frames])
+        epoch = cond.get(COND_EPOCH)
+        if eng.cond_current(epoch):
+            eng.bind(sh.local(idx, B), None, None, epoch=epoch)
+        else:
+            ctx = cond["crossattn"].float()
+            eng.bind(sh.local(idx, B), sh.local(ctx, B), loc(cond["dense_vector"]), ctx0=ctx[::num_frames], epoch=epoch)
         eng.run()
         out_l = torch.empty_like(blended)
         ops.denoise_finish(eng.eps, blended, loc(c_out), out_l, nl, h, w)
@@ -217,6 +223,23 @@ class ConstantGuidance(object):
         return uncond + scale * (cond - uncond)
 
 
+_CAT_KEYS = ("vector", "crossattn", "concat", "replace", "dense_vector")  # seva/sampling.py:234
+COND_EPOCH = "_cond_epoch"  # private key of the prepared conditioning dict (ignored by the reference's SGMWrapper)
+_EPOCHS = itertools.count(1)
+
+
+def _version(t) -> int:
+    try:
+        return t._version
+    except RuntimeError:  # inference tensors do not track versions
+        return -1
+
+
+def _same_cond(a: list, b: list) -> bool:
+    return len(a) == len(b) and all(p[0] == q[0] and p[1] is q[1] and p[2] is q[2] and p[3:] == q[3:]
+                                    for p, q in zip(a, b))
+
+
 class VanillaCFG(object):
     def __init__(self):
         self.scale_rule = ConstantScaleRule()
@@ -230,14 +253,26 @@ class VanillaCFG(object):
         return self.guidance(x_u, x_c, scale_value)
 
     def prepare_inputs(self, x: torch.Tensor, s: torch.Tensor, c: dict, uc: dict):
-        c_out = dict()
+        """[uncond; cond] stacking (sampling.py:231-242).  The stacked conditioning does not change inside a
+        sampling loop, so it is built once per (c, uc) and loop -- the sampler drops the cache in
+        ``prepare_sampling_loop`` -- and tagged with a ``_cond_epoch`` the denoiser hands to the launch plan,
+        which then skips its conditioning-only launches.  A fresh dict is returned every call: the
+        denoiser pops ``replace`` from it (sampling.py:147)."""
+        ident = [(k, c[k], uc[k], _version(c[k]), _version(uc[k])) for k in c if k in _CAT_KEYS]
+        cache = self.__dict__.get("_cond_cache")
+        if cache is None or not _same_cond(cache[0], ident):
+            c_out = {k: torch.cat((u, v), 0) for k, v, u, _, _ in ident}
+            c_out[COND_EPOCH] = next(_EPOCHS)
+            cache = self.__dict__["_cond_cache"] = (ident, c_out)  # holds c / uc alive: identities stay unique
+        c_out = dict(cache[1])
         for k in c:
-            if k in ["vector", "crossattn", "concat", "replace", "dense_vector"]:
-                c_out[k] = torch.cat((uc[k], c[k]), 0)
-            else:
+            if k not in _CAT_KEYS:
                 assert c[k] == uc[k]
                 c_out[k] = c[k]
         return torch.cat([x] * 2), torch.cat([s] * 2), c_out
+
+    def reset_cache(self) -> None:
+        self.__dict__.pop("_cond_cache", None)
 
     def frame_scale(self, x: torch.Tensor, sigma: torch.Tensor, scale, **guider_kwargs) -> torch.Tensor | None:
         """Per-frame guidance scale [T] (fp32) for the fused combine+Euler kernel; None if not expressible."""
@@ -313,6 +348,9 @@ class EulerEDMSampler(object):
         num_sigmas = len(sigmas)
         s_in = x.new_ones([x.shape[0]])
         self._scale_cache = None
+        reset = getattr(self.guider, "reset_cache", None)
+        if reset is not None:  # conditioning may have been rewritten in place since the last loop
+            reset()
         return x, s_in, sigmas, num_sigmas, cond, uc
 
     def get_sigma_gen(self, num_sigmas: int, verbose: bool = True):

@@ -162,6 +162,57 @@ def test_sampler_api_quirks(tiny):
     assert "replace" not in cond  # popped from the per-step dict (:147)
 
 
+def test_step_invariant_hoisting_is_exact_and_refreshes(tiny):
+    """inside a sampling loop the stacked conditioning is built once and the plan skips its
+    conditioning-only launches; the result must equal the un-hoisted loop bit for bit, and a conditioning rewritten
+    in place between two loops (same tensor objects) must be picked up by the second loop."""
+    from seva_b200 import sampling as S
+
+    P, model, sd, g, inp = tiny
+    guider = S.MultiviewCFG(1.2)
+    x_h, _ = _sample_ours(model, inp, 3, 3, 2.0, guider)
+    eng = next(iter(model.module._engines.values()))
+    assert eng._skip_invariant and len(eng._invariant) >= 3 and eng.n_launch_step < eng.n_launch
+
+    class NoHoist(S.MultiviewCFG):  # rebuilds the conditioning every step, like the reference
+        def prepare_inputs(self, x, s, c, uc):
+            self.reset_cache()
+            return super().prepare_inputs(x, s, c, uc)
+
+    x_n, _ = _sample_ours(model, inp, 3, 3, 2.0, NoHoist(1.2))
+    assert not eng._skip_invariant
+    assert torch.equal(x_h, x_n)
+
+    # same cond objects, contents rewritten between loops
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device="cuda")
+    sampler = S.EulerEDMSampler(disc, guider, num_steps=2, s_churn=0.0, s_tmin=0.0, s_tmax=999.0, s_noise=1.0,
+                                verbose=False, device="cuda")
+    c, uc = to_dev(inp["c"]), to_dev(inp["uc"])
+    kw = dict(c2w=inp["c2w"].cuda(), K=inp["K"].cuda(), input_frame_mask=inp["mask"].cuda())
+    den = lambda input, sigma, cc: denoiser(model, input, sigma, cc, num_frames=3)
+
+    def loop():
+        torch.manual_seed(0)
+        with torch.inference_mode(), torch.autocast("cuda"):
+            return sampler(den, inp["x0"].clone().cuda(), scale=2.0, cond=c, uc=uc, verbose=False, **kw).clone()
+
+    a = loop()
+    c["crossattn"].mul_(-1.0)
+    c["dense_vector"].mul_(0.5)
+    b = loop()
+    fresh, _ = None, None
+    sampler2 = S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), num_steps=2, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
+                                 s_noise=1.0, verbose=False, device="cuda")
+    torch.manual_seed(0)
+    with torch.inference_mode(), torch.autocast("cuda"):
+        model.module._engines.clear()  # a plan that has never seen the first conditioning
+        fresh = sampler2(den, inp["x0"].clone().cuda(), scale=2.0, cond={k: v.clone() for k, v in c.items()},
+                         uc=uc, verbose=False, **kw)
+    assert not torch.equal(a, b)
+    assert torch.equal(b, fresh)
+
+
 @pytest.mark.skipif(not os.path.exists(os.path.join(GOLD, "config1.npz")), reason="config1 golden not generated")
 def test_config1_full_model_one_step_vs_reference():
     """BASELINE config 1: Seva 1.3B random-init, T=8 (1 input + 7 targets) @576x576, one Euler-EDM step."""

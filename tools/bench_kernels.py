@@ -50,3 +50,12 @@ if which in ("all", "gemv"):
         o = torch.empty(M, N_, device=dev)
         t = timeit(lambda: ops.gemv_rows(x, W, b, silu_in=True, out=o))
         print(f"gemv M={M} N={N_} K={K}: {t*1e3:.1f} us")
+if which in ("all", "step"):
+    # the fused CFG-combine + Euler update moves ~10 MB at T=21 (latency-bound); the x64 batch (T=1344)
+    # makes the HBM figure meaningful.  bytes = x, uncond, cond read + x_next written, fp32.
+    for T in (21, 1344):
+        x = torch.randn(T, 4, 72, 72, device=dev); den = torch.randn(2 * T, 4, 72, 72, device=dev)
+        sc = torch.full((T,), 2.0, device=dev); s0 = torch.full((T,), 3.0, device=dev); s1 = torch.full((T,), 2.5, device=dev)
+        out = torch.empty_like(x)
+        t = timeit(lambda: ops.cfg_euler_step(x, den, sc, s0, s1, out=out))
+        print(f"cfg_euler_step T={T}: {t*1e3:.1f} us {4*x.numel()*4/t/1e6:.0f} GB/s")
