@@ -254,6 +254,7 @@ class Seva(nn.Module):
             self._engines[key] = eng
         return eng
 
+    @torch.compiler.disable  # a launch plan of hand-written kernels: opaque to torch.compile(MODEL) (demo.py:63)
     def forward(self, x: torch.Tensor, t: torch.Tensor, y: torch.Tensor, dense_y: torch.Tensor,
                 num_frames: int | None = None, cond_epoch=None) -> torch.Tensor:
         """``cond_epoch`` (optional, from the guider's prepared conditioning): y / dense_y are unchanged since the
@@ -292,6 +293,7 @@ class SGMWrapper(nn.Module):
         super().__init__()
         self.module = module
 
+    @torch.compiler.disable  # nothing here for a tracing compiler: one cat, then the launch plan
     def forward(self, x: torch.Tensor, t: torch.Tensor, c: dict, **kwargs) -> torch.Tensor:
         concat = c.get("concat", None)
         if concat is not None and concat.numel() > 0:

@@ -88,6 +88,7 @@ class DDPMDiscretization(object):
 def _is_fused_network(network) -> bool:
     from .model import SGMWrapper, Seva
 
+    network = getattr(network, "_orig_mod", network)  # torch.compile(MODEL) wrapper (demo.py:63)
     return isinstance(network, SGMWrapper) and isinstance(network.module, Seva)
 
 
@@ -130,7 +131,7 @@ class DiscreteDenoiser(object):
 
     def _call_fused(self, network, input, sigma, cond, num_frames=None, **extra):
         """Same arithmetic as above with the elementwise work fused around the network plan."""
-        module = network.module
+        module = getattr(network, "_orig_mod", network).module
         num_frames = num_frames or module.params.num_frames
         n, _, h, w = input.shape
         with torch.autocast("cuda", enabled=False):

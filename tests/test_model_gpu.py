@@ -162,6 +162,24 @@ def test_sampler_api_quirks(tiny):
     assert "replace" not in cond  # popped from the per-step dict (:147)
 
 
+def test_torch_compile_wrapper_is_tolerated(tiny):
+    """demo.py:63 wraps MODEL in torch.compile on nightly builds: the wrapper must reach the same launch plan
+    (fused denoiser path and plain ``network(x, t, c)`` call), not trace it."""
+    from seva_b200 import sampling as S
+
+    P, model, sd, g, inp = tiny
+    compiled = torch.compile(model, dynamic=False)
+    assert S._is_fused_network(compiled)
+    x_e, _ = _sample_ours(model, inp, 3, 2, 2.0, S.MultiviewCFG(1.2))
+    x_c, _ = _sample_ours(compiled, inp, 3, 2, 2.0, S.MultiviewCFG(1.2))
+    assert torch.equal(x_e, x_c)
+    cc = to_dev({k: torch.cat((inp["uc"][k], inp["c"][k]), 0) for k in ("crossattn", "concat", "dense_vector")})
+    with torch.inference_mode(), torch.autocast("cuda"):
+        a = model(g["net_in"].cuda(), g["net_t"].cuda(), cc, num_frames=3)
+        b = compiled(g["net_in"].cuda(), g["net_t"].cuda(), cc, num_frames=3)
+    assert torch.equal(a, b)
+
+
 def test_step_invariant_hoisting_is_exact_and_refreshes(tiny):
     """inside a sampling loop the stacked conditioning is built once and the plan skips its
     conditioning-only launches; the result must equal the un-hoisted loop bit for bit, and a conditioning rewritten
