@@ -162,6 +162,61 @@ def test_sampler_api_quirks(tiny):
     assert "replace" not in cond  # popped from the per-step dict (:147)
 
 
+def test_tracked_sampler_subclass_matches_builtin_loop(tiny):
+    """The Gradio front end subclasses the sampler and drives the public pieces itself (eval.py:1040-1089:
+    prepare_sampling_loop -> get_sigma_gen -> sampler_step, polling an abort event between steps).  That loop must
+    give the built-in loop's latents bit for bit, and an abort must return to Python after the current step."""
+    import threading
+
+    from seva_b200 import sampling as S
+
+    P, model, sd, g, inp = tiny
+
+    class Tracked(S.EulerEDMSampler):
+        def __init__(self, abort_event, *a, **k):
+            super().__init__(*a, **k)
+            self.abort_event, self.ticks = abort_event, 0
+
+        def __call__(self, denoiser, x, scale, cond, uc=None, num_steps=None, verbose=True, **kw):
+            uc = cond if uc is None else uc
+            x, s_in, sigmas, n, cond, uc = self.prepare_sampling_loop(x, cond, uc, num_steps)
+            for i in self.get_sigma_gen(n, verbose=verbose):
+                churn = min(self.s_churn / (n - 1), 2**0.5 - 1) if self.s_tmin <= sigmas[i] <= self.s_tmax else 0.0
+                x = self.sampler_step(s_in * sigmas[i], s_in * sigmas[i + 1], denoiser, x, scale, cond, uc, churn, **kw)
+                self.ticks += 1
+                if self.abort_event.is_set():
+                    return None
+            return x
+
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device="cuda")
+    args = dict(num_steps=3, s_churn=0.0, s_tmin=0.0, s_tmax=999.0, s_noise=1.0, verbose=False, device="cuda")
+    kw = dict(c2w=inp["c2w"].cuda(), K=inp["K"].cuda(), input_frame_mask=inp["mask"].cuda())
+    den = lambda input, sigma, cc: denoiser(model, input, sigma, cc, num_frames=3)
+
+    def run(sampler):
+        torch.manual_seed(3)
+        with torch.inference_mode(), torch.autocast("cuda"):
+            return sampler(den, inp["x0"].clone().cuda(), scale=2.0, cond=to_dev(inp["c"]), uc=to_dev(inp["uc"]),
+                           verbose=False, **kw)
+
+    ev = threading.Event()
+    base = run(S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), **args))
+    tracked = Tracked(ev, disc, S.MultiviewCFG(1.2), **args)
+    out = run(tracked)
+    assert tracked.ticks == 3 and torch.equal(out, base)
+    ev.set()
+    tracked.ticks = 0
+    assert run(tracked) is None and tracked.ticks == 1
+    # the same loop from a worker thread (demo_gr.py:659-687 renders on a daemon thread)
+    ev.clear()
+    box = {}
+    th = threading.Thread(target=lambda: box.setdefault("x", run(tracked)), daemon=True)
+    th.start()
+    th.join(120)
+    assert not th.is_alive() and torch.equal(box["x"], base)
+
+
 def test_torch_compile_wrapper_is_tolerated(tiny):
     """demo.py:63 wraps MODEL in torch.compile on nightly builds: the wrapper must reach the same launch plan
     (fused denoiser path and plain ``network(x, t, c)`` call), not trace it."""
