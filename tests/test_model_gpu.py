@@ -93,6 +93,31 @@ def test_guidance_bookkeeping_bit_exact():
         assert torch.equal(den.sigma_to_idx(sch[f"sigmas_{n}"][:-1] + 1e-6), sch[f"idx_{n}"])
 
 
+def test_bookkeeping_kernels_fuzz_vs_oracle():
+    """Integer / boolean bookkeeping on the GPU against the oracle on seeded windows that sit on the rule's thresholds
+    (rotation 9.99 / 10.01 degrees, translation 5e-6 / 2e-5, changed focal length) and on sigmas at table entries,
+    midpoints and one ulp off: bit-exact.  The same generator is checked against the live reference by
+    oracle/fuzz_oracle.py in the build container."""
+    from oracle.fuzz_oracle import threshold_window
+    from seva_b200 import sampling as S
+
+    gen = torch.Generator().manual_seed(11)
+    rule = S.MultiviewScaleRule(1.2)
+    for i in range(150):
+        T, c2w, K, mask = threshold_window(gen, i)
+        want = O.close_frame(c2w, K, mask)
+        got = rule.close_frame(c2w.cuda(), K.cuda(), mask.cuda()).cpu()
+        assert torch.equal(got, want), (i, got, want)
+        assert torch.equal(rule(2.0, c2w.cuda(), K.cuda(), mask.cuda()).cpu(), O.multiview_scale(2.0, 1.2, c2w, K, mask))
+    den = S.DiscreteDenoiser(S.DDPMDiscretization(), num_idx=1000, device="cuda")
+    table = O.denoiser_table()
+    for _ in range(50):
+        k = torch.randint(0, 999, (64,), generator=gen)
+        s = torch.cat([torch.exp(torch.rand(256, generator=gen) * 9.0 - 4.0), table[k], 0.5 * (table[k] + table[k + 1]),
+                       table[k] * (1 + 1e-7), table[k] * (1 - 1e-7)])
+        assert torch.equal(den.sigma_to_idx(s.cuda()).cpu(), O.sigma_to_idx(table, s))
+
+
 def test_tiny_network_vs_reference_and_oracle(tiny):
     P, model, sd, g, inp = tiny
     T = 3
