@@ -330,6 +330,37 @@ def test_config1_full_model_one_step_vs_reference():
     assert e_x < NET_TOL, e_x
 
 
+@pytest.mark.parametrize("T,n_in,h,w", [(4, 1, 16, 24), (5, 2, 24, 16), (2, 1, 8, 40), (7, 3, 32, 16)])
+def test_ragged_shapes_two_steps_vs_oracle(T, n_in, h, w):
+    """Non-square latents, odd frame counts and several input frames through the public sampler (ray map from the
+    CUDA Plucker kernel) vs the fp32 oracle on the same draws: per-step denoiser output and final latents."""
+    from seva_b200 import geometry as G
+    from seva_b200 import sampling as S
+    from seva_b200.model import SevaParams
+
+    P = SevaParams(model_channels=64, num_frames=T)
+    model, sd = build_model(P, seed=T)
+    steps = 2
+    inp = synth.make_inputs(T, n_in, h, w, O.plucker, seed=3, num_steps=steps, ctx_dim=P.context_dim)
+    pl = G.get_plucker_coordinates(inp["w2c"][0].cuda(), inp["w2c"].cuda(), intrinsics=inp["K"].clone().cuda(),
+                                   target_size=[h, w]).cpu()
+    assert (pl - inp["plucker"]).abs().max().item() < 1e-4
+    x, cap = _sample_ours(model, inp, T, steps, 2.0, S.MultiviewCFG(1.2))
+    table = O.denoiser_table()
+    fs = O.multiview_scale(2.0, 1.2, inp["c2w"], inp["K"], inp["mask"])
+    net = lambda xx, idx, c: O.sgm_forward(sd, P, xx, idx, c, num_frames=T)
+    with torch.inference_mode():
+        sig = torch.cat([O.ddpm_sigmas(steps), torch.zeros(1)])
+        x0 = inp["x0"] * torch.sqrt(1.0 + sig[0] ** 2.0)
+        ones = torch.ones(T)
+        _, den0 = O.sampler_step(net, table, x0, ones * sig[0], ones * sig[1], fs, inp["c"], inp["uc"], inp["eps"][0])
+        ref = O.sample(net, table, inp["x0"], fs, inp["c"], inp["uc"], steps, inp["eps"])
+    u, c = cap[0].float().cpu().chunk(2)
+    den_ours = u + fs.view(-1, 1, 1, 1) * (c - u)
+    assert rel_l2(den_ours, den0) < NET_TOL, rel_l2(den_ours, den0)
+    assert rel_l2(x, ref) < FINAL_TOL, rel_l2(x, ref)
+
+
 def test_tiny_50_steps_final_latents_vs_oracle(tiny):
     """north_star: final latents within rel-L2 5e-2 of the fp32 reference after the full 50-step schedule (tiny network
     here; tools/parity_50step.py runs the same check at BASELINE configs[1] size against the oracle on the GPU)."""
