@@ -113,6 +113,24 @@ def main() -> int:
         worst_p = max(worst_p, (want - got).abs().max().item())
     bad += (worst_d > 1e-3) + (worst_p > 1e-5)
     print(f"camera_dist: max abs diff {worst_d:.2e} (degrees / units); plucker: max abs diff {worst_p:.2e}")
+    # network restatement vs the reference modules on several small configurations (model.py:176-234)
+    from oracle import synth
+    worst_n = 0.0
+    for mc, T, h, w, heads_ch in ((32, 2, 8, 8, 32), (32, 3, 16, 24, 32), (64, 5, 24, 16, 64), (64, 4, 16, 16, 32)):
+        P = R.model.SevaParams(model_channels=mc, num_frames=T, num_head_channels=heads_ch)
+        torch.manual_seed(mc + T)
+        net = R.model.SGMWrapper(R.model.Seva(P).eval())
+        sd = {k: v.detach().clone() for k, v in net.module.state_dict().items()}
+        inp = synth.make_inputs(T, 1, h, w, O.plucker, seed=T, num_steps=1, ctx_dim=P.context_dim)
+        cc = {k: torch.cat((inp["uc"][k], inp["c"][k]), 0) for k in ("crossattn", "concat", "dense_vector")}
+        x = torch.randn(2 * T, 4, h, w, generator=g)
+        t = torch.randint(0, 1000, (1,), generator=g).repeat(2 * T)
+        with torch.inference_mode():
+            want = net(x, t, cc, num_frames=T)
+            got = O.sgm_forward(sd, P, x, t, cc, num_frames=T)
+        worst_n = max(worst_n, ((want - got).norm() / want.norm()).item())
+    bad += worst_n > 1e-5
+    print(f"network forward (4 small configurations incl. non-square latents): max rel-L2 {worst_n:.2e}")
     return int(bad > 0)
 
 
