@@ -171,6 +171,10 @@ def test_no_cpu_fallback():
     with pytest.raises(_lib.SevaB200Error):
         m(torch.zeros(6, 11, 16, 16), torch.zeros(6, dtype=torch.long), torch.zeros(6, 1, 1024),
           torch.zeros(6, 6, 16, 16), num_frames=3)
+    from seva_b200.model import SevaParams
+    for bad in (dict(num_head_channels=32), dict(model_channels=96)):  # unsupported configurations fail at construction
+        with pytest.raises(_lib.SevaB200Error):
+            Seva(SevaParams(**bad))
     if not torch.cuda.is_available():
         assert _lib.load().seva_check_device() != 0
         assert "no CPU fallback" in _lib.last_error() or "sm_100a" in _lib.last_error()
