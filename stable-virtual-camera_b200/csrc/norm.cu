@@ -543,6 +543,55 @@ layernorm_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, __nv_bfloat
   }
 }
 
+// Same arithmetic with half a warp per row and 8-byte accesses (C % 64 == 0, 8-byte aligned rows): a warp keeps two
+// rows in flight and issues half as many memory instructions.  Lane l of the half-warp owns channels
+// [4 (16 k + l), 4 (16 k + l) + 4), k < NP.
+template <int NP>
+__global__ void __launch_bounds__(256)
+layernorm_half_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y,
+                      long long ldy, const float* __restrict__ gamma, const float* __restrict__ beta, int M,
+                      int C, float eps, int reverse) {
+  const int half = threadIdx.x >> 4, l = threadIdx.x & 15;
+  const long long row = (long long)(reverse ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * 16 + half;
+  const bool live = row < M;  // both halves of a warp take part in the shuffles
+  const uint2* xp = reinterpret_cast<const uint2*>(x + (live ? row : 0) * ldx);
+  float v[4 * NP];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const uint2 u = __ldg(xp + k * 16 + l);
+    v[4 * k] = bf16_lo(u.x);
+    v[4 * k + 1] = bf16_hi(u.x);
+    v[4 * k + 2] = bf16_lo(u.y);
+    v[4 * k + 3] = bf16_hi(u.y);
+    s += (v[4 * k] + v[4 * k + 1]) + (v[4 * k + 2] + v[4 * k + 3]);
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4 * NP; ++k) {
+    const float d = v[k] - mean;
+    q = fmaf(d, d, q);
+  }
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  if (!live) return;
+  const float rstd = rsqrtf(q / (float)C + eps);
+  uint2* yp = reinterpret_cast<uint2*>(y + row * ldy);
+  const float4* g4 = reinterpret_cast<const float4*>(gamma);
+  const float4* b4 = reinterpret_cast<const float4*>(beta);
+#pragma unroll
+  for (int k = 0; k < NP; ++k) {
+    const float4 g = __ldg(g4 + k * 16 + l), b = __ldg(b4 + k * 16 + l);
+    uint2 o;
+    o.x = pack_bf16x2(fmaf((v[4 * k] - mean) * rstd, g.x, b.x), fmaf((v[4 * k + 1] - mean) * rstd, g.y, b.y));
+    o.y = pack_bf16x2(fmaf((v[4 * k + 2] - mean) * rstd, g.z, b.z), fmaf((v[4 * k + 3] - mean) * rstd, g.w, b.w));
+    yp[k * 16 + l] = o;
+  }
+}
+
 // generic fallback (any even C): three passes over the row through L1/L2
 __global__ void __launch_bounds__(256)
 layernorm_generic_kernel(const __nv_bfloat16* __restrict__ x, long long ldx,
@@ -723,7 +772,17 @@ extern "C" int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, 
   const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
   const int grid = (M + 7) / 8;
-  if (C == 320)
+  const bool wide = (ldx % 4) == 0 && (ldy % 4) == 0 && (((uintptr_t)x | (uintptr_t)y) & 7) == 0 &&
+                    (((uintptr_t)gamma | (uintptr_t)beta) & 15) == 0;
+  const int grid16 = (M + 15) / 16;
+#define SEVA_LN_HALF(NP_) \
+  layernorm_half_kernel<NP_><<<grid16, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps, reverse != 0)
+  if (wide && C == 320) SEVA_LN_HALF(5);
+  else if (wide && C == 640) SEVA_LN_HALF(10);
+  else if (wide && C == 64) SEVA_LN_HALF(1);
+  else if (wide && C == 128) SEVA_LN_HALF(2);
+  else if (wide && C == 256) SEVA_LN_HALF(4);
+  else if (C == 320)
     layernorm_kernel<5><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps, reverse != 0);
   else if (C == 640)
     layernorm_kernel<10><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps, reverse != 0);
@@ -737,6 +796,7 @@ extern "C" int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, 
     layernorm_kernel<4><<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps, reverse != 0);
   else
     layernorm_generic_kernel<<<grid, 256, 0, stream>>>(xp, ldx, yp, ldy, gamma, beta, M, C, eps, reverse != 0);
+#undef SEVA_LN_HALF
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
