@@ -150,3 +150,46 @@ def test_run_scene_two_ranks_equals_one_rank():
         for r in range(2):
             assert torch.equal(ret[r]["two_pass"], want2), f"rank {r}: chunk-parallel second pass differs"
             assert torch.equal(ret[r]["one_pass"], want1), f"rank {r}: chained one-pass differs"
+
+
+def test_prepared_conditioning_cache_host_logic():
+    """SURVEY 8f N2 host side: the stacked conditioning is built once per (c, uc) and sampling loop, tagged with an
+    epoch, rebuilt when a tensor is replaced or (where versions are tracked) written in place, and dropped by
+    prepare_sampling_loop; the per-step dict is always a fresh one (the denoiser pops 'replace' from it)."""
+    import torch
+
+    from seva_b200 import sampling as S
+
+    T = 3
+    c = {"crossattn": torch.randn(T, 1, 8), "replace": torch.randn(T, 5, 4, 4), "concat": torch.randn(T, 7, 4, 4),
+         "dense_vector": torch.randn(T, 6, 4, 4)}
+    uc = {k: torch.zeros_like(v) for k, v in c.items()}
+    g = S.MultiviewCFG(1.2)
+    x, s = torch.randn(T, 4, 4, 4), torch.ones(T)
+    xa, sa, a = g.prepare_inputs(x, s, c, uc)
+    xb, sb, b = g.prepare_inputs(x, s, c, uc)
+    assert xa.shape[0] == 2 * T and sa.shape[0] == 2 * T
+    assert a is not b and a[S.COND_EPOCH] == b[S.COND_EPOCH]
+    for k in c:
+        assert a[k] is b[k] and torch.equal(a[k], torch.cat((uc[k], c[k]), 0))  # uncond first (sampling.py:236)
+    a.pop("replace")
+    assert "replace" in g.prepare_inputs(x, s, c, uc)[2]
+    c["crossattn"].mul_(2.0)  # in-place write: version counter moves
+    d = g.prepare_inputs(x, s, c, uc)[2]
+    assert d[S.COND_EPOCH] != a[S.COND_EPOCH] and torch.equal(d["crossattn"][T:], c["crossattn"])
+    c2 = dict(c, concat=c["concat"].clone())  # replaced tensor object
+    e = g.prepare_inputs(x, s, c2, uc)[2]
+    assert e[S.COND_EPOCH] != d[S.COND_EPOCH]
+    with torch.inference_mode():  # inference tensors track no version: identity only, reset between loops
+        ci = {k: v.clone() for k, v in c.items()}
+        f1 = g.prepare_inputs(x, s, ci, uc)[2]
+        f2 = g.prepare_inputs(x, s, ci, uc)[2]
+        assert f1[S.COND_EPOCH] == f2[S.COND_EPOCH]
+        sampler = S.EulerEDMSampler(S.DDPMDiscretization(), g, num_steps=2, device="cpu")
+        sampler.prepare_sampling_loop(x.clone(), ci, uc)
+        assert g.prepare_inputs(x, s, ci, uc)[2][S.COND_EPOCH] != f1[S.COND_EPOCH]
+    # non-tensor keys pass through and must agree between c and uc (sampling.py:238-239)
+    c3, uc3 = dict(c, tag=1), dict(uc, tag=1)
+    assert g.prepare_inputs(x, s, c3, uc3)[2]["tag"] == 1
+    with pytest.raises(AssertionError):
+        g.prepare_inputs(x, s, c3, dict(uc, tag=2))
