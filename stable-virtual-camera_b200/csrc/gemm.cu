@@ -53,6 +53,7 @@ struct GemmArgs {
   int dbg;
   int reverse;  // 1: walk the tile list backwards (L2-aware traversal, see seva_b200.h)
   int fast;  // 1: bf16 output, N % 32 == 0 and 16-byte aligned pointers/strides -> coalesced epilogue
+  int wstat;  // 1: weight-stationary walk (opt-in): the CTA's N tile of W stays in smem for all of its M tiles
 };
 
 // ---- GEGLU: x * gelu(g), exact (erf) GELU --------------------------------------------------------------
@@ -246,13 +247,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t bar_tfull = smem_base + 16 * kMaxStages;   // 2 x 8 B
   const uint32_t bar_tempty = bar_tfull + 16;               // 2 x 8 B
   const uint32_t tmem_slot = bar_tempty + 16;               // 4 B
+  const uint32_t bar_bfull = bar_tempty + 24;               // 8 B (weight-stationary mode: W tile landed)
   const uint32_t patch_base = smem_base + kCtrlBytes;       // kEpiWarps x kPatchBytes
   const uint32_t bias_base = patch_base + kEpiWarps * kPatchBytes;   // kEpiWarps x kBiasSlotBytes
   const uint32_t tiles_base = bias_base + kEpiWarps * kBiasSlotBytes;
   const uint32_t a_bytes = BM * BK * 2;
   const uint32_t b_rows = a.bn / kCtas;
   const uint32_t b_bytes = b_rows * BK * 2;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
+  // Weight-stationary mode (one CTA, one tap, short K; the launcher sizes the grid as a multiple of n_tiles, so the
+  // tile walk below gives every CTA the same N tile each time): W's [bn, K] tile is loaded once into kchunks
+  // swizzled slabs ahead of the ring, and the ring carries A only.
+  const uint32_t wstat_bytes = a.wstat ? a.kchunks * b_bytes : 0u;
+  const uint32_t stage_bytes = a.wstat ? a_bytes : a_bytes + b_bytes;
+  const uint32_t ring_base = tiles_base + wstat_bytes;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -271,6 +278,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, kEpiWarps * kCtas);
     }
+    mbar_init(bar_bfull, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -291,6 +299,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     {   // all 32 lanes run the (warp-uniform) loop so that addresses stay in uniform registers;
         // one elected lane issues the TMA instructions
       uint32_t it_g = 0, s = 0, ph = 0;
+      if (kCtas == 1 && a.wstat && cluster_id < a.num_tiles) {
+        const int pt0 = a.reverse ? a.num_tiles - 1 - cluster_id : cluster_id;
+        const int n0 = (pt0 % a.n_tiles) * a.bn;
+        if (elect_one()) {
+          mbar_expect_tx(bar_bfull, wstat_bytes);
+          for (int kc = 0; kc < a.kchunks; ++kc)
+            tma_load_2d(tiles_base + kc * b_bytes, &tmB, bar_bfull, kc * BK, n0);
+        }
+        __syncwarp();
+      }
       for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters) {
         const int pt = a.reverse ? a.num_tiles - 1 - tile : tile;
         const int m0 = (pt / a.n_tiles) * (BM * kCtas) + rank * BM;
@@ -300,10 +318,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (a.ntaps == 9) off = (tap / 3 - 1) * a.tap_wp + (tap % 3 - 1);
           for (int kc = 0; kc < a.kchunks; ++kc, ++it_g) {
             mbar_wait(bar_empty + 8 * s, ph ^ 1);
-            const uint32_t sa = tiles_base + s * stage_bytes;
+            const uint32_t sa = ring_base + s * stage_bytes;
             if (elect_one()) {
               if ((a.dbg & 1) && it_g >= (uint32_t)a.stages) {
                 if (rank == 0) mbar_arrive(bar_full + 8 * s);
+              } else if (kCtas == 1 && a.wstat) {
+                mbar_expect_tx(bar_full + 8 * s, a_bytes);
+                tma_load_2d(sa, &tmA, bar_full + 8 * s, kc * BK, m0 + off);
               } else if (kCtas == 2) {
                 // both CTAs' bytes are counted on the leader's barrier (the MMA issuer waits there)
                 const uint32_t fb = mapa_cluster(bar_full + 8 * s, 0);
@@ -334,6 +355,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (rank == 0) {   // whole warp loops (uniform); one elected lane issues
       const uint32_t idesc = make_idesc_bf16(BM * kCtas, a.bn, 0, 0);
       uint32_t tl = 0, s = 0, ph = 0;
+      if (kCtas == 1 && a.wstat && cluster_id < a.num_tiles) mbar_wait(bar_bfull, 0);
       for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
         const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
         mbar_wait(bar_tempty + 8 * as, aph ^ 1);
@@ -342,9 +364,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int it = 0; it < iters; ++it) {
           if (!(a.dbg & 4)) mbar_wait(bar_full + 8 * s, ph);
           tc_fence_after();
-          const uint32_t sa = tiles_base + s * stage_bytes;
+          const uint32_t sa = ring_base + s * stage_bytes;
           const uint64_t adesc = make_sdesc_sw128(sa, 16, 1024);
-          const uint64_t bdesc = make_sdesc_sw128(sa + a_bytes, 16, 1024);
+          const uint64_t bdesc = make_sdesc_sw128((kCtas == 1 && a.wstat) ? tiles_base + it * b_bytes : sa + a_bytes, 16, 1024);
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
@@ -672,6 +694,24 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   const int fixed = kCtrlBytes + 1024 + kEpiWarps * (kPatchBytes + kBiasSlotBytes);
   int stages = (kSmemMax - fixed) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
+  // Weight-stationary walk (SEVA_WSTAT=0 turns it off): short-K single-tap problems whose [bn, K] weight tile and
+  // at least 3 A stages fit; the grid becomes a multiple of n_tiles so that a CTA keeps one N tile.  Measured at
+  // M = 217728, K = 320: N = 960 170.8 -> 154.3 us, N = 320 68.4 -> 64.3 us (108.4 -> 104.4 with a residual).
+  a.wstat = 0;
+  int wstat_bytes = 0, wstat_grid = 0;
+  {
+    static int want = -1;
+    if (want < 0) { const char* e = getenv("SEVA_WSTAT"); want = e ? atoi(e) : 1; }
+    const int a_bytes = BM * BK * 2, wb = a.kchunks * bn * BK * 2;
+    if (want && ctas == 1 && g->ntaps == 1 && (g->Kc % BK) == 0 && a.n_tiles <= sms && m_tiles >= 2 * (sms / a.n_tiles) &&
+        fixed + wb + 3 * a_bytes <= kSmemMax) {
+      a.wstat = 1;
+      wstat_bytes = wb;
+      wstat_grid = (sms / a.n_tiles) * a.n_tiles;
+      stages = (kSmemMax - fixed - wb) / a_bytes;
+      if (stages > kMaxStages) stages = kMaxStages;
+    }
+  }
   a.stages = stages;
 
   CUtensorMap tmA, tmB;
@@ -688,7 +728,7 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
     if (make_tmap_bf16(&tmB, g->W, 2, dims, strides, box)) return 4;
   }
 
-  const int smem = fixed + stages * stage_bytes;
+  const int smem = a.wstat ? fixed + wstat_bytes + stages * (BM * BK * 2) : fixed + stages * stage_bytes;
   static bool attr_set = false;
   if (!attr_set) {
     SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
@@ -698,6 +738,7 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   if (ctas == 1) {
     int grid = sms;
     if (grid > a.num_tiles) grid = a.num_tiles;
+    if (a.wstat) grid = wstat_grid;
     gemm_kernel<1><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
   } else {
     int pairs = sms / 2;

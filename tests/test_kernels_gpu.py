@@ -63,6 +63,24 @@ def test_gemm_strided_residual_rowbias_fp32out(ops):
     assert rel_l2(out32, A.float() @ W.float().t() + b) < 1e-4
 
 
+@pytest.mark.parametrize("M,N,reverse", [(19021, 320, False), (19021, 320, True), (8000, 960, False), (30001, 640, True)])
+def test_gemm_weight_stationary_walk(ops, M, N, reverse):
+    """Tall K = 320 problems take the weight-stationary walk (the CTA's N tile of W loaded once, grid a multiple of the
+    N-tile count): bias + per-image bias + residual epilogue, ragged last M tile, both traversal directions."""
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    K, rpi = 320, 997
+    A = bf(torch.randn(M, K, device="cuda", generator=g))
+    W = bf(torch.randn(N, K, device="cuda", generator=g) / math.sqrt(K))
+    b = torch.randn(N, device="cuda", generator=g)
+    res = bf(torch.randn(M, N, device="cuda", generator=g))
+    rb = torch.randn((M + rpi - 1) // rpi, N, device="cuda", generator=g)
+    out = ops.linear(A, W, b, residual=res, rowbias=rb, rowbias_rpi=rpi, reverse=reverse)
+    ref = A.float() @ W.float().t() + b + res.float() + rb[torch.arange(M, device="cuda") // rpi]
+    assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
+    plain = ops.linear(A, W, None)
+    assert rel_l2(plain, A.float() @ W.float().t()) < 5e-3
+
+
 @pytest.mark.parametrize("M,K,inner", [(777, 320, 1280), (300, 640, 2560)])
 def test_gemm_geglu(ops, M, K, inner):
     from seva_b200 import pack
