@@ -134,20 +134,22 @@ def _worker(rank, world, port, ret):
         dist.destroy_process_group()
 
 
-def test_run_scene_two_ranks_equals_one_rank():
+@pytest.mark.parametrize("world", [2, 3])
+def test_run_scene_two_ranks_equals_one_rank(world):
+    """7 second-pass windows over 2 ranks (4 + 3) and 3 ranks (3 + 2 + 2): every rank ends with the one-rank result."""
     sc, T, opts = _scene_1_to_n()
     want2, want1 = _run(sc, T, opts, SC.Rank()), _run(sc, T, opts, SC.Rank(), one_pass=True)
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         ret = mgr.dict()
         port = _free_port()
-        procs = [ctx.Process(target=_worker, args=(r, 2, port, ret)) for r in range(2)]
+        procs = [ctx.Process(target=_worker, args=(r, world, port, ret)) for r in range(world)]
         for p in procs:
             p.start()
         for p in procs:
-            p.join(180)
+            p.join(240)
             assert p.exitcode == 0, f"worker exit code {p.exitcode}"
-        for r in range(2):
+        for r in range(world):
             assert torch.equal(ret[r]["two_pass"], want2), f"rank {r}: chunk-parallel second pass differs"
             assert torch.equal(ret[r]["one_pass"], want1), f"rank {r}: chained one-pass differs"
 
