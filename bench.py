@@ -10,8 +10,13 @@ ours       one "step" = one Euler-EDM sampler step with MultiviewCFG (CFG batch 
            inside the timed region.  N > 1: one process per GPU, each rank samples its own independent T-frame
            chunk (the two-pass procedure's second-pass chunks, SURVEY.md section 8e) - no data-path collective;
            the timed region is bracketed by barrier + synchronize and the max over ranks is used (weak scaling).
-reference  the reference algorithm on the box's host cores: the oracle port (plain PyTorch fp32, all threads) -
-           the Python reference itself cannot travel to the GPU box - on a bounded sample of the workload.
+           The line also carries `cpu_baseline` (one step of the reference's own code on the host cores) and
+           `gpu_library_baseline` (the unmodified reference modules in eager PyTorch, bf16 autocast, on the same GPU).
+reference  the REFERENCE's own implementation of the path (oracle/_ref, staged by oracle/make_ref.py: the
+           unmodified seva/{model,sampling,geometry}.py + seva/modules/{layers,transformer}.py) on the box's host
+           cores, fp32, all threads, at the FULL workload (T=21, CFG batch 42).  A step costs minutes, so the run is
+           bounded by --cpu-budget seconds (at least one timed step; the line reports the steps actually timed).
+           Falls back to the oracle port (and says so in cpu_baseline.kind) only when oracle/_ref is absent.
 Prints ONE JSON line.
 """
 from __future__ import annotations
@@ -34,7 +39,6 @@ import torch  # noqa: E402
 
 # Algorithmic FLOPs of the reference graph per CFG'd step (FlopCounterMode)
 REF_TFLOP_PER_STEP = {8: 26.336, 21: 76.912, 64: 314.534}
-CPU_SAMPLE_T = 6  # frames in the bounded CPU sample (~15 s per step on 16 threads)
 
 
 def measured_peaks():
@@ -82,6 +86,18 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": sm[len(sm) // 2] if sm else None,
                 "sm_max_mhz": float(self.samples[0][1]) if self.samples else None,
                 "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+def chunk_parallelism(world):
+    return f"dp{world}: one independent T-frame chunk per rank, no data-path collective"
+
+
+def workload_config(T, h, w, parallelism):
+    """`config` of both arms (identical workload string: the driver compares them)."""
+    return {"workload": f"Seva 1.3B random-init, T={T} @{h * 8}x{w * 8} (latent {h}x{w}), Euler-EDM step with "
+                        f"MultiviewCFG (CFG batch {2 * T}), configs[1]",
+            "parallelism": parallelism,
+            "l2": "activations per step (>2 GB) exceed the 126 MB L2; no explicit flush"}
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -135,7 +151,7 @@ def run_ours(args):
     # --parallel cfg:    ONE chunk; uncond / cond halves on rank pairs, remaining factor world/2 splits the frames
     # --parallel frames: ONE chunk; all ranks split the frames (K/V exchanged at 3D / time-mix attention)
     guider = S.MultiviewCFG(1.2)
-    chunks_world, par_desc = world, f"dp{world} (one independent T-frame chunk per GPU)" if world > 1 else "single GPU"
+    chunks_world, par_desc = world, chunk_parallelism(world)
     if world > 1 and args.parallel != "chunks":
         from seva_b200 import dist as D
 
@@ -283,18 +299,26 @@ def run_ours(args):
     value = chunks_world * T * steps / (ms_dev / 1e3)
     e2e_v = chunks_world * T * steps / (ms_e2e / 1e3)
     tf_step = REF_TFLOP_PER_STEP.get(T)
+    lib = None
+    n_launch_step = eng.n_launch_step
+    if world == 1 and not args.no_gpu_baseline:
+        model.module.invalidate()  # return our workspaces before the reference modules allocate theirs
+        del eng
+        torch.cuda.empty_cache()
+        try:
+            lib = gpu_library_baseline(T, h, w, dev)
+        except Exception as e:  # a baseline leg must never take the product line down
+            lib = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
+        torch.cuda.empty_cache()
     cpu = cpu_baseline(args) if world == 1 and not args.no_cpu else None
     line = {
         "metric": "frame-steps/s", "value": round(value, 3), "unit": "frame-steps/s", "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": round(ms_dev / steps, 3), "higher_is_better": True,
         "scaling": "weak" if chunks_world == world else "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"Seva 1.3B random-init, T={T} @{h * 8}x{w * 8} (latent {h}x{w}), Euler-EDM step with "
-                               f"MultiviewCFG (CFG batch {2 * T}), configs[1]",
-                   "parallelism": par_desc,
-                   "l2": "activations per step (>2 GB) exceed the 126 MB L2; no explicit flush"},
+        "config": workload_config(T, h, w, par_desc),
         "e2e": {"value": round(e2e_v, 3), "unit": "frame-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e / steps, 3)},
-        "gpu_launches": eng.n_launch_step * steps + 4 * steps,
+        "gpu_launches": n_launch_step * steps + 4 * steps,
         "clocks": clk, "roofline": roof, "ms_per_step_with_launch_events": round(ms_inst / steps, 3),
         "step_tflops": round(chunks_world * tf_step * steps / (ms_dev / 1e3), 1) if tf_step else None,
         "step_frac_of_peak": round(chunks_world * tf_step * steps / (ms_dev / 1e3) / peaks["tf_sustained"] / world, 4)
@@ -303,6 +327,8 @@ def run_ours(args):
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if lib is not None:
+        line["gpu_library_baseline"] = lib
     print(json.dumps(line))
 
 
@@ -407,13 +433,46 @@ def run_scene_bench(args):
             "clocks": clk, "latent_checksum": round(float(out.double().abs().mean()), 6)}))
 
 
-def cpu_step_sample(T, h, w, threads):
-    """One Euler-EDM step of the oracle port (plain PyTorch fp32) on the host cores; returns seconds."""
+def _reference_rig(device, T, h, w):
+    """The REFERENCE's own objects for the path (oracle/_ref staged by oracle/make_ref.py, or /root/reference):
+    SGMWrapper(Seva(SevaParams())) with default-init weights (seed 0), DiscreteDenoiser, EulerEDMSampler with
+    MultiviewCFG(1.2), and the synthetic chunk of SURVEY.md 8d.  Returns None when neither copy exists."""
+    from oracle import refimport, synth
+
+    if not (refimport.available() or refimport.staged_available()):
+        return None
+    ref = refimport.import_staged()
+    M, S, G = ref.model, ref.sampling, ref.geometry
+    torch.manual_seed(0)
+    net = M.SGMWrapper(M.Seva(M.SevaParams()).eval()).to(device)
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device=device)
+    sampler = S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), num_steps=50, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
+                                s_noise=1.0, verbose=False, device=device)
+    plk = lambda s_, e_, K_, hh, ww: G.get_plucker_coordinates(extrinsics_src=s_, extrinsics=e_, intrinsics=K_,
+                                                               target_size=(hh, ww))
+    inp = synth.make_inputs(T, 1, h, w, plk, seed=1, num_steps=1)
+    mv = lambda d: {k: v.to(device) for k, v in d.items()}
+    sig = disc(50, device=device)
+    ones = torch.ones(T, device=device)
+    x = inp["x0"].to(device) * 84.9222
+    c, uc = mv(inp["c"]), mv(inp["uc"])
+    kw = dict(c2w=inp["c2w"].to(device), K=inp["K"].to(device), input_frame_mask=inp["mask"].to(device))
+    den = lambda i_, s_, c_: denoiser(net, i_, s_, c_, num_frames=T)
+
+    def step(i):
+        k = i % 50
+        return sampler.sampler_step(ones * sig[k], ones * sig[k + 1], den, x, 2.0, c, uc, 0.0, **kw)
+
+    return step, ref.root
+
+
+def _port_rig(T, h, w):
+    """Fallback when the reference copy is absent: the oracle PORT (plain PyTorch fp32 restatement)."""
     from oracle import seva_oracle as O
     from oracle import synth
     from seva_b200.model import Seva, SevaParams
 
-    torch.set_num_threads(threads)
     P = SevaParams()
     with torch.device("meta"):
         m = Seva(P)
@@ -427,42 +486,106 @@ def cpu_step_sample(T, h, w, threads):
     sig = torch.cat([O.ddpm_sigmas(50), torch.zeros(1)])
     ones = torch.ones(T)
     net = lambda x, idx, c: O.sgm_forward(sd, P, x, idx, c, num_frames=T)
+
+    def step(i):
+        k = i % 50
+        return O.sampler_step(net, table, inp["x0"] * 84.9222, ones * sig[k], ones * sig[k + 1], fs, inp["c"], inp["uc"],
+                              inp["eps"][0])[0]
+
+    return step
+
+
+def cpu_reference_run(T, h, w, steps, warmup, budget_s):
+    """Times the reference's CPU implementation of the path on all host cores, fp32: ``EulerEDMSampler.sampler_step``
+    of the staged reference at the FULL workload (T frames, CFG batch 2T).  One step costs minutes at T=21, so the
+    run is bounded: at most ``steps`` timed steps, stopping once ``budget_s`` is spent (always at least one); warm-up
+    steps only while they fit the same budget.  Returns (seconds per step, steps timed, warm-ups done, kind, cores)."""
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    rig = _reference_rig(torch.device("cpu"), T, h, w)
+    kind = "reference"
+    if rig is None:
+        step, kind = _port_rig(T, h, w), "port"
+    else:
+        step = rig[0]
+    times, n_warm, out = [], 0, None
+    t_start = time.time()
     with torch.inference_mode():
-        t0 = time.time()
-        O.sampler_step(net, table, inp["x0"] * 84.9222, ones * sig[0], ones * sig[1], fs, inp["c"], inp["uc"], inp["eps"][0])
-        return time.time() - t0
+        est = None
+        for i in range(warmup):
+            if est is not None and (time.time() - t_start) + 2 * est > budget_s:
+                break
+            t0 = time.time()
+            out = step(i)
+            est = time.time() - t0
+            if (time.time() - t_start) + est > budget_s:  # a warm-up that would eat the only timed step: count it as timed
+                times.append(est)
+                break
+            n_warm += 1
+        for i in range(steps):
+            if times and (time.time() - t_start) + times[-1] > budget_s:
+                break
+            t0 = time.time()
+            out = step(n_warm + i)
+            times.append(time.time() - t0)
+    assert out is not None and torch.isfinite(out).all()
+    return sum(times) / len(times), len(times), n_warm, kind, threads
 
 
 def cpu_baseline(args):
-    threads = os.cpu_count() or 1
-    secs = cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads)
-    return {"value": round(CPU_SAMPLE_T / secs, 5), "unit": "frame-steps/s", "cores": threads, "kind": "port",
-            "sample": f"one Euler-EDM step of the oracle port (PyTorch fp32, {threads} threads) at T={CPU_SAMPLE_T} "
-                      f"@{args.size * 8}x{args.size * 8} (CFG batch {2 * CPU_SAMPLE_T}); {secs:.1f} s; per-frame cost at "
-                      f"T={args.T} is higher (3D attention grows with T^2)"}
+    """`cpu_baseline` of the product line: a bounded sample (ONE step) of the same workload on the host cores."""
+    secs, n, _, kind, threads = cpu_reference_run(args.T, args.size, args.size, 1, 0, args.cpu_budget)
+    what = ("the reference's own EulerEDMSampler.sampler_step (oracle/_ref copy of seva/{model,sampling,geometry}.py + "
+            "modules)" if kind == "reference" else "the oracle port (reference copy absent)")
+    return {"value": round(args.T / secs, 5), "unit": "frame-steps/s", "cores": threads, "kind": kind,
+            "sample": f"{n} Euler-EDM step with MultiviewCFG of {what}, PyTorch fp32, {threads} threads, at the full "
+                      f"workload T={args.T} @{args.size * 8}x{args.size * 8} (CFG batch {2 * args.T}); {secs:.1f} s/step"}
+
+
+def gpu_library_baseline(T, h, w, device, steps=3):
+    """the reference modules themselves on the SAME B200 in eager PyTorch under bf16
+    autocast (library kernels: cuBLAS / cuDNN / the flash SDPA the reference forces, transformer.py:70) - the honest
+    GPU baseline next to our kernels.  One warm-up step, then ``steps`` steps between CUDA events."""
+    rig = _reference_rig(device, T, h, w)
+    if rig is None:
+        return {"unavailable": "reference copy (oracle/_ref) not staged"}
+    step = rig[0]
+    with torch.inference_mode(), torch.autocast("cuda", dtype=torch.bfloat16):
+        step(0)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            out = step(1 + i)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    assert torch.isfinite(out).all()
+    return {"value": round(T / (ms / 1e3), 3), "unit": "frame-steps/s", "ms_per_step": round(ms, 2), "steps": steps,
+            "what": "UNMODIFIED reference modules (oracle/_ref: seva.model / seva.sampling), eager PyTorch, "
+                    "torch.autocast(bf16), forced FLASH SDPA, same GPU, same workload, inputs resident in HBM"}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    threads = os.cpu_count() or 1
-    times = []
-    for _ in range(min(args.warmup, 1)):
-        cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads)
-    for _ in range(max(1, min(args.steps, 3))):
-        times.append(cpu_step_sample(CPU_SAMPLE_T, args.size, args.size, threads))
-    secs = sum(times) / len(times)
-    v = round(CPU_SAMPLE_T / secs, 5)
+    secs, n, n_warm, kind, threads = cpu_reference_run(args.T, args.size, args.size, max(1, args.steps), args.warmup,
+                                                       args.cpu_budget)
+    v = round(args.T / secs, 5)
     world = int(os.environ.get("WORLD_SIZE", 1))
+    h = w = args.size
+    what = ("reference's own code (oracle/_ref: seva.sampling.EulerEDMSampler.sampler_step -> DiscreteDenoiser -> "
+            "SGMWrapper(Seva) -> MultiviewCFG)" if kind == "reference" else "oracle port (reference copy absent)")
     print(json.dumps({
         "impl": "reference", "metric": "frame-steps/s", "value": v, "unit": "frame-steps/s", "n_gpus": world,
-        "steps": len(times), "warmup": min(args.warmup, 1), "ms_per_step": round(secs * 1e3, 1), "higher_is_better": True,
+        "steps": n, "warmup": n_warm, "ms_per_step": round(secs * 1e3, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"Seva 1.3B random-init, T={args.T} @{args.size * 8}x{args.size * 8}, Euler-EDM step with "
-                               f"MultiviewCFG, configs[1]; each step is a bounded sample (T={CPU_SAMPLE_T} frames)"},
-        "cpu_baseline": {"value": v, "unit": "frame-steps/s", "cores": threads, "kind": "port",
-                         "sample": f"oracle port (PyTorch fp32) one Euler-EDM step at T={CPU_SAMPLE_T}, {secs:.1f} s/step"},
+        "config": workload_config(args.T, h, w, chunk_parallelism(world)),  # identical to the product arm's at this N
+        "cpu_baseline": {"value": v, "unit": "frame-steps/s", "cores": threads, "kind": kind,
+                         "sample": f"{what}, PyTorch fp32 on {threads} host threads at the full workload T={args.T} "
+                                   f"(CFG batch {2 * args.T}); {n} timed step(s) of {secs:.1f} s after {n_warm} warm-up "
+                                   f"(bounded to ~{args.cpu_budget:.0f} s: requested --steps {args.steps} --warmup {args.warmup})"},
         "e2e": {"value": v, "unit": "frame-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -480,6 +603,9 @@ if __name__ == "__main__":
     ap.add_argument("--workload", default="step", choices=["step", "scene"],
                     help="step: one Euler-EDM step of configs[1] (the driver's contract); scene: configs[2] end to end")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the eager-PyTorch reference-on-GPU leg")
+    ap.add_argument("--cpu-budget", type=float, default=float(os.environ.get("SEVA_CPU_BUDGET_S", 300)),
+                    help="seconds the CPU reference leg may spend (it always times at least one full step)")
     ap.add_argument("--dump-launches", default=None, help="write per-launch CUDA-event timings (JSON) here")
     a = ap.parse_args()
     if a.impl == "reference":

@@ -8,10 +8,36 @@ import sys
 import types
 
 REFERENCE_ROOT = os.environ.get("SEVA_REFERENCE_ROOT", "/root/reference")
+STAGED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")  # oracle/make_ref.py (hot path only)
 
 
 def available() -> bool:
     return os.path.isdir(os.path.join(REFERENCE_ROOT, "seva"))
+
+
+def staged_available() -> bool:
+    return os.path.exists(os.path.join(STAGED_ROOT, "seva", "sampling.py"))
+
+
+def import_staged():
+    """The reference's hot-path modules from ``oracle/_ref`` (the copy ``oracle/make_ref.py`` stages for the GPU box;
+    the full tree at /root/reference is preferred when it exists).  Used by bench.py's reference arm and
+    ``gpu_library_baseline`` leg only."""
+    root = REFERENCE_ROOT if available() else STAGED_ROOT
+    if not (available() or staged_available()):
+        raise RuntimeError(f"reference not found at {REFERENCE_ROOT} nor staged at {STAGED_ROOT} (run oracle/make_ref.py)")
+    if "roma" not in sys.modules:
+        try:
+            __import__("roma")
+        except Exception:
+            sys.modules["roma"] = types.ModuleType("roma")
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    import seva.geometry as geometry
+    import seva.model as model
+    import seva.sampling as sampling
+
+    return types.SimpleNamespace(model=model, sampling=sampling, geometry=geometry, root=root)
 
 
 def import_reference():
