@@ -462,24 +462,16 @@ extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* 
   a.ldo = ldo;
   a.bso = bso;
   a.scale_log2 = scale * 1.4426950408889634f;
-  // developer knobs: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_PING = 0 / 1
-  static int emu = -1, ping = kPingDefault;
-  if (emu < 0) {
-    const char* e = getenv("SEVA_ATTN_EMU");
-    emu = e ? atoi(e) : kEmuDefault;
-    const char* pg = getenv("SEVA_ATTN_PING");
-    if (pg) ping = atoi(pg);
-  }
   dim3 grid((Lq + 255) / 256, Hh, B);
-#define SEVA_ATTN_LAUNCH(E, P)                                                                               \
-  {                                                                                                          \
-    static bool attr = false;                                                                                \
-    if (!attr) {                                                                                             \
-      SEVA_CUDA(cudaFuncSetAttribute(attn_kernel<E, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem)); \
-      attr = true;                                                                                           \
-    }                                                                                                        \
-    attn_kernel<E, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);                          \
+#define SEVA_ATTN_LAUNCH(E, P)                                                                      \
+  {                                                                                                 \
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(attn_kernel<E, P>), kAttnSmem)) return 2;     \
+    attn_kernel<E, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);                 \
   }
+#ifdef SEVA_DEBUG
+  // developer builds only: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_PING = 0 / 1
+  static const int emu = [] { const char* e = getenv("SEVA_ATTN_EMU"); return e ? atoi(e) : kEmuDefault; }();
+  static const int ping = [] { const char* e = getenv("SEVA_ATTN_PING"); return e ? atoi(e) : kPingDefault; }();
   if (ping) {
     switch (emu) {
       case 0: SEVA_ATTN_LAUNCH(0, true) break;
@@ -497,6 +489,9 @@ extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* 
       default: SEVA_ATTN_LAUNCH(4, false) break;
     }
   }
+#else
+  SEVA_ATTN_LAUNCH(kEmuDefault, (kPingDefault != 0))  // the one release instantiation
+#endif
 #undef SEVA_ATTN_LAUNCH
   SEVA_CUDA(cudaGetLastError());
   return 0;

@@ -7,6 +7,9 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+#include <vector>
+
 #include "../../include/seva_b200.h"
 
 namespace seva {
@@ -79,6 +82,28 @@ static DevInfo& dev_info() {
     d.valid = 1;
   }
   return d;
+}
+
+int ensure_dyn_smem(const void* func, int bytes) {
+  struct Entry { const void* f; int dev; int bytes; };
+  static std::mutex mu;
+  static std::vector<Entry> done;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    set_error("cudaGetDevice failed");
+    return 2;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  for (const Entry& e : done)
+    if (e.f == func && e.dev == dev && e.bytes >= bytes) return 0;
+  cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(MaxDynamicSharedMemorySize=%d) failed on device %d: %s", bytes, dev,
+              cudaGetErrorString(e));
+    return 2;
+  }
+  done.push_back({func, dev, bytes});
+  return 0;
 }
 
 int sm_count() { return dev_info().sms > 0 ? dev_info().sms : 148; }

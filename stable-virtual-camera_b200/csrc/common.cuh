@@ -35,6 +35,9 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t*
                    const uint64_t* strides_bytes, const uint32_t* box);
 int sm_count();
 int check_device();  // 0 when the current device is sm_100
+// Opt a kernel in to `bytes` of dynamic shared memory on the CURRENT device.  The attribute is per device, so the
+// "done" flag is kept per (function, device); thread-safe.  Returns 0 on success (message via set_error otherwise).
+int ensure_dyn_smem(const void* func, int bytes);
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------------

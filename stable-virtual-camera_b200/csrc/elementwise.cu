@@ -437,92 +437,97 @@ timestep_embedding_kernel(const long long* __restrict__ t, float* __restrict__ o
   if ((dim & 1) && k == 0) out[(long long)n * dim + dim - 1] = 0.f;
 }
 
-// out[m, n] = act(x[m, :]) . W[n, :] + bias[n].  A block owns 8 rows of x (staged in smem, fp32) and 128 output
-// columns, ONE COLUMN PER THREAD: the x values are warp-wide broadcast reads (one wavefront per LDS.128) and every
-// 16-byte weight load feeds 64 FMAs, so the kernel is FMA-bound.  (The first version gave each lane a k-slice of one
-// column: 2 LDS.128 with distinct addresses per 8 FMAs made it shared-memory bound, 450 us for the 22 time-embedding
-// projections at M = 42.)  A thread walks its own weight row; the eight 16-byte pieces of a 128-byte line are used by
-// consecutive iterations and hit in L1.
-// Grouped form: blockIdx.z selects one of `count` independent problems (descriptor table in device memory),
-// so the ~90 tiny per-step GEMVs (time-embedding projections, single-token cross-attention) are 3 launches.
-constexpr int kGemvRows = 8;
-constexpr int kGemvCols = 128;
+// out[m, n] = act(x[m, :]) . W[n, :] + bias[n] for a handful of rows m (time-embedding MLP, the 22 emb_layers, the
+// single-token cross-attention vectors): weight-bandwidth work.  A WARP owns kGwCols output columns and the lanes split
+// K, so every weight load is a coalesced 16-byte-per-lane read of a contiguous 512-byte run and each weight element is
+// fetched from L2 once per kGwRows rows; the fp32 x rows (L1-resident, ~200 KB) are read once per kGwCols columns.
+// Per pass (kGwRows rows x kGwCols columns): K/256 trips of 4 + 16 loads and 256 FMAs per lane, then a butterfly
+// reduction.  (The previous kernel walked one weight row per THREAD with the x rows in shared memory: a serial chain
+// of 160 dependent 16-byte loads per column -- 456 us for the 22 emb_layers at M = 42 against ~60 MB of weights.)
+// Grouped form: blockIdx.y selects one of `count` independent problems (descriptor table in device memory), so the
+// ~90 tiny per-step GEMVs are 3 launches.
+constexpr int kGwCols = 4;
+constexpr int kGwRows = 8;
+constexpr int kGwWarps = 8;   // 32 columns per block
 
-__device__ __forceinline__ void gemv_tile(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
-                                          const float* __restrict__ bias, float* __restrict__ out, int M, int N,
-                                          int K, int silu_in, int silu_out, float* xs) {
-  const int m0 = blockIdx.y * kGemvRows;
-  if (m0 >= M || (int)blockIdx.x * kGemvCols >= N) return;
-  const int rows = min(kGemvRows, M - m0);
-  const int K4 = K >> 2;
-  const float4* x4 = reinterpret_cast<const float4*>(x + (long long)m0 * K);
-  float4* xs4 = reinterpret_cast<float4*>(xs);
-#pragma unroll 4
-  for (int i = threadIdx.x; i < kGemvRows * K4; i += blockDim.x) {
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i < rows * K4) {
-      v = __ldg(x4 + i);
-      if (silu_in) {
-        v.x = v.x / (1.0f + __expf(-v.x));
-        v.y = v.y / (1.0f + __expf(-v.y));
-        v.z = v.z / (1.0f + __expf(-v.z));
-        v.w = v.w / (1.0f + __expf(-v.w));
+__device__ __forceinline__ float silu_exact(float v) { return v / (1.0f + __expf(-v)); }
+
+__device__ __forceinline__ void gemv_warp_tile(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
+                                               const float* __restrict__ bias, float* __restrict__ out, int M, int N,
+                                               int K, int silu_in, int silu_out) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = ((int)blockIdx.x * kGwWarps + warp) * kGwCols;
+  if (n0 >= N) return;
+  const __nv_bfloat16* wrow[kGwCols];
+#pragma unroll
+  for (int c = 0; c < kGwCols; ++c) wrow[c] = W + (long long)min(n0 + c, N - 1) * K;
+  for (int m0 = 0; m0 < M; m0 += kGwRows) {
+    float acc[kGwRows][kGwCols];
+#pragma unroll
+    for (int r = 0; r < kGwRows; ++r)
+#pragma unroll
+      for (int c = 0; c < kGwCols; ++c) acc[r][c] = 0.f;
+    for (int k0 = lane * 8; k0 < K; k0 += 256) {
+      float wv[kGwCols][8];
+#pragma unroll
+      for (int c = 0; c < kGwCols; ++c) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4*>(wrow[c] + k0));
+        wv[c][0] = bf16_lo(u.x); wv[c][1] = bf16_hi(u.x); wv[c][2] = bf16_lo(u.y); wv[c][3] = bf16_hi(u.y);
+        wv[c][4] = bf16_lo(u.z); wv[c][5] = bf16_hi(u.z); wv[c][6] = bf16_lo(u.w); wv[c][7] = bf16_hi(u.w);
+      }
+#pragma unroll
+      for (int r = 0; r < kGwRows; ++r) {
+        if (m0 + r < M) {  // warp-uniform
+          const float4* xp = reinterpret_cast<const float4*>(x + (long long)(m0 + r) * K + k0);
+          float4 a = __ldg(xp), b = __ldg(xp + 1);
+          if (silu_in) {
+            a.x = silu_exact(a.x); a.y = silu_exact(a.y); a.z = silu_exact(a.z); a.w = silu_exact(a.w);
+            b.x = silu_exact(b.x); b.y = silu_exact(b.y); b.z = silu_exact(b.z); b.w = silu_exact(b.w);
+          }
+#pragma unroll
+          for (int c = 0; c < kGwCols; ++c) {
+            float t = acc[r][c];
+            t = fmaf(wv[c][0], a.x, t); t = fmaf(wv[c][1], a.y, t); t = fmaf(wv[c][2], a.z, t); t = fmaf(wv[c][3], a.w, t);
+            t = fmaf(wv[c][4], b.x, t); t = fmaf(wv[c][5], b.y, t); t = fmaf(wv[c][6], b.z, t); t = fmaf(wv[c][7], b.w, t);
+            acc[r][c] = t;
+          }
+        }
       }
     }
-    xs4[i] = v;
-  }
-  __syncthreads();
-  const int n = blockIdx.x * kGemvCols + threadIdx.x;
-  const bool active = n < N;
-  float acc[kGemvRows];
 #pragma unroll
-  for (int r = 0; r < kGemvRows; ++r) acc[r] = 0.f;
-  const uint4* wr = reinterpret_cast<const uint4*>(W + (long long)(active ? n : 0) * K);
-#pragma unroll 2
-  for (int k8 = 0; k8 < (K >> 3); ++k8) {
-    const uint4 u = __ldg(wr + k8);
-    const float wv[8] = {bf16_lo(u.x), bf16_hi(u.x), bf16_lo(u.y), bf16_hi(u.y),
-                         bf16_lo(u.z), bf16_hi(u.z), bf16_lo(u.w), bf16_hi(u.w)};
+    for (int r = 0; r < kGwRows; ++r)
 #pragma unroll
-    for (int r = 0; r < kGemvRows; ++r) {
-      const float4 x0 = xs4[r * K4 + 2 * k8];
-      const float4 x1 = xs4[r * K4 + 2 * k8 + 1];
-      acc[r] = fmaf(wv[0], x0.x, acc[r]);
-      acc[r] = fmaf(wv[1], x0.y, acc[r]);
-      acc[r] = fmaf(wv[2], x0.z, acc[r]);
-      acc[r] = fmaf(wv[3], x0.w, acc[r]);
-      acc[r] = fmaf(wv[4], x1.x, acc[r]);
-      acc[r] = fmaf(wv[5], x1.y, acc[r]);
-      acc[r] = fmaf(wv[6], x1.z, acc[r]);
-      acc[r] = fmaf(wv[7], x1.w, acc[r]);
-    }
-  }
-  if (!active) return;
-  const float bv = bias != nullptr ? bias[n] : 0.f;
+      for (int c = 0; c < kGwCols; ++c) {
+        float t = acc[r][c];
 #pragma unroll
-  for (int r = 0; r < kGemvRows; ++r) {
-    if (r < rows) {
-      float v = acc[r] + bv;
-      if (silu_out) v = v / (1.0f + __expf(-v));
-      out[(long long)(m0 + r) * N + n] = v;
-    }
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        acc[r][c] = t;
+      }
+    // lane l < kGwRows * kGwCols stores element (r = l / kGwCols, c = l % kGwCols): 4 consecutive floats per row
+#pragma unroll
+    for (int r = 0; r < kGwRows; ++r)
+#pragma unroll
+      for (int c = 0; c < kGwCols; ++c)
+        if (lane == r * kGwCols + c && m0 + r < M && n0 + c < N) {
+          float v = acc[r][c] + (bias != nullptr ? bias[n0 + c] : 0.f);
+          if (silu_out) v = silu_exact(v);
+          out[(long long)(m0 + r) * N + n0 + c] = v;
+        }
   }
 }
 
-__global__ void __launch_bounds__(kGemvCols)
+__global__ void __launch_bounds__(kGwWarps * 32)
 gemv_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ W,
                  const float* __restrict__ bias, float* __restrict__ out, int M, int N, int K, int silu_in,
                  int silu_out) {
-  extern __shared__ float xs[];  // [kGemvRows][K]
-  gemv_tile(x, W, bias, out, M, N, K, silu_in, silu_out, xs);
+  gemv_warp_tile(x, W, bias, out, M, N, K, silu_in, silu_out);
 }
 
-__global__ void __launch_bounds__(kGemvCols)
+__global__ void __launch_bounds__(kGwWarps * 32)
 gemv_grouped_kernel(const SevaGemvProblem* __restrict__ probs) {
-  extern __shared__ float xs[];
-  const SevaGemvProblem p = probs[blockIdx.z];
-  gemv_tile(p.x, reinterpret_cast<const __nv_bfloat16*>(p.W), p.bias, p.out, p.M, p.N, p.K, p.silu_in,
-            p.silu_out, xs);
+  const SevaGemvProblem p = probs[blockIdx.y];
+  gemv_warp_tile(p.x, reinterpret_cast<const __nv_bfloat16*>(p.W), p.bias, p.out, p.M, p.N, p.K, p.silu_in,
+                 p.silu_out);
 }
 
 inline unsigned blocks_for(long long total, int threads) {
@@ -722,17 +727,10 @@ extern "C" int seva_gemv_rows(const float* x, const void* W, const float* bias, 
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
   SEVA_CHECK(x && W && out, "seva_gemv_rows: null pointer");
   SEVA_CHECK(M > 0 && N > 0 && K > 0 && (K % 8) == 0, "seva_gemv_rows: need K %% 8 == 0");
-  SEVA_CHECK(K * kGemvRows * 4 <= 200 * 1024, "seva_gemv_rows: K too large (%d)", K);
-  const size_t smem = sizeof(float) * kGemvRows * K;
-  static size_t smem_set = 0;
-  if (smem > 48 * 1024 && smem > smem_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(gemv_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   200 * 1024));
-    smem_set = 200 * 1024;
-  }
-  dim3 grid((N + kGemvCols - 1) / kGemvCols, (M + kGemvRows - 1) / kGemvRows);
-  gemv_rows_kernel<<<grid, kGemvCols, smem, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M,
-                                                N, K, silu_in, silu_out);
+  SEVA_CHECK((((uintptr_t)x | (uintptr_t)W) & 15) == 0, "seva_gemv_rows: x and W must be 16-byte aligned");
+  const int cols_per_block = kGwWarps * kGwCols;
+  gemv_rows_kernel<<<(N + cols_per_block - 1) / cols_per_block, kGwWarps * 32, 0, stream>>>(
+      x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M, N, K, silu_in, silu_out);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }
@@ -742,15 +740,10 @@ extern "C" int seva_gemv_grouped(const SevaGemvProblem* problems_dev, int32_t co
   if (check_device()) return 3;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
   SEVA_CHECK(problems_dev && count > 0 && max_M > 0 && max_N > 0 && max_K > 0, "seva_gemv_grouped: bad arguments");
-  SEVA_CHECK((max_K % 8) == 0 && max_K * kGemvRows * 4 <= 200 * 1024, "seva_gemv_grouped: K must be a multiple of 8 and <= 6400");
-  const size_t smem = sizeof(float) * kGemvRows * max_K;
-  static size_t smem_set = 0;
-  if (smem > 48 * 1024 && smem > smem_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(gemv_grouped_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    smem_set = 200 * 1024;
-  }
-  dim3 grid((max_N + kGemvCols - 1) / kGemvCols, (max_M + kGemvRows - 1) / kGemvRows, count);
-  gemv_grouped_kernel<<<grid, kGemvCols, smem, stream>>>(problems_dev);
+  SEVA_CHECK((max_K % 8) == 0 && count <= 65535, "seva_gemv_grouped: K must be a multiple of 8, count <= 65535");
+  const int cols_per_block = kGwWarps * kGwCols;
+  dim3 grid((max_N + cols_per_block - 1) / cols_per_block, count);
+  gemv_grouped_kernel<<<grid, kGwWarps * 32, 0, stream>>>(problems_dev);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

@@ -39,6 +39,14 @@ constexpr int kPatchBytes = 4096;        // per-epilogue-warp transpose patch: 3
 constexpr int kBiasSlotBytes = 512;      // per-epilogue-warp column constants of the current tile (128 fp32)
 constexpr int kMaxStages = 8;
 
+// Developer knobs (skip TMA loads / barrier waits / epilogue stores for pipeline A/B measurements) exist only in
+// -DSEVA_DEBUG builds: the shipped kernel cannot be told to skip work through the environment.
+#ifdef SEVA_DEBUG
+#define SEVA_DBG(a, bit) (((a).dbg & (bit)) != 0)
+#else
+#define SEVA_DBG(a, bit) false
+#endif
+
 struct GemmArgs {
   int M, N, Nout, Kc, ntaps, tap_wp, kchunks;
   int bn, n_tiles, num_tiles, stages;
@@ -320,7 +328,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             mbar_wait(bar_empty + 8 * s, ph ^ 1);
             const uint32_t sa = ring_base + s * stage_bytes;
             if (elect_one()) {
-              if ((a.dbg & 1) && it_g >= (uint32_t)a.stages) {
+              if (SEVA_DBG(a, 1) && it_g >= (uint32_t)a.stages) {
                 if (rank == 0) mbar_arrive(bar_full + 8 * s);
               } else if (kCtas == 1 && a.wstat) {
                 mbar_expect_tx(bar_full + 8 * s, a_bytes);
@@ -362,7 +370,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * 256;
         for (int it = 0; it < iters; ++it) {
-          if (!(a.dbg & 4)) mbar_wait(bar_full + 8 * s, ph);
+          if (!SEVA_DBG(a, 4)) mbar_wait(bar_full + 8 * s, ph);
           tc_fence_after();
           const uint32_t sa = ring_base + s * stage_bytes;
           const uint64_t adesc = make_sdesc_sw128(sa, 16, 1024);
@@ -525,7 +533,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld32(taddr + c * 32, v);
           tmem_wait_ld();
           if (c == u_end - 1) release_tmem();
-          if (!live || (a.dbg & 2)) continue;
+          if (!live || SEVA_DBG(a, 2)) continue;
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
@@ -559,7 +567,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld32(taddr + a.bn / 2 + p * 32, vg);
           tmem_wait_ld();
           if (p == u_end - 1) release_tmem();
-          if (a.dbg & 2) continue;
+          if (SEVA_DBG(a, 2)) continue;
           float f[32], g[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
@@ -672,11 +680,14 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.Wp = g->Wp;
   a.reverse = g->reverse != 0;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+#ifdef SEVA_DEBUG
   {
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("SEVA_GEMM_DEBUG"); dbg = e ? atoi(e) : 0; }
+    static const int dbg = [] { const char* e = getenv("SEVA_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     a.dbg = dbg;
   }
+#else
+  a.dbg = 0;
+#endif
   a.fast = !g->out_fp32 && (a.Nout % 32) == 0 && (g->N % 32) == 0 && (g->ldo % 8) == 0 && al16(g->out) &&
            (g->bias == nullptr || al16(g->bias)) && (g->rowbias == nullptr || al16(g->rowbias)) &&
            (g->residual == nullptr || ((g->ldr % 8) == 0 && al16(g->residual)));
@@ -700,8 +711,11 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.wstat = 0;
   int wstat_bytes = 0, wstat_grid = 0;
   {
-    static int want = -1;
-    if (want < 0) { const char* e = getenv("SEVA_WSTAT"); want = e ? atoi(e) : 1; }
+#ifdef SEVA_DEBUG
+    static const int want = [] { const char* e = getenv("SEVA_WSTAT"); return e ? atoi(e) : 1; }();
+#else
+    constexpr int want = 1;
+#endif
     const int a_bytes = BM * BK * 2, wb = a.kchunks * bn * BK * 2;
     if (want && ctas == 1 && g->ntaps == 1 && (g->Kc % BK) == 0 && a.n_tiles <= sms && m_tiles >= 2 * (sms / a.n_tiles) &&
         fixed + wb + 3 * a_bytes <= kSmemMax) {
@@ -729,12 +743,9 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   }
 
   const int smem = a.wstat ? fixed + wstat_bytes + stages * (BM * BK * 2) : fixed + stages * stage_bytes;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
-    SEVA_CUDA(cudaFuncSetAttribute(gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemMax));
-    attr_set = true;
-  }
+  if (ensure_dyn_smem(ctas == 1 ? reinterpret_cast<const void*>(gemm_kernel<1>) : reinterpret_cast<const void*>(gemm_kernel<2>),
+                      kSmemMax))
+    return 2;
   if (ctas == 1) {
     int grid = sms;
     if (grid > a.num_tiles) grid = a.num_tiles;

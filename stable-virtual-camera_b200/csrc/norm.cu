@@ -747,11 +747,7 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   if (p->dense) {
     const size_t smem_d = ((smem + 15) & ~(size_t)15) + (size_t)kGnRing * threads * 8 + (size_t)a.pix_per_block * 24;
     SEVA_CHECK(smem_d <= 200 * 1024, "seva_groupnorm_apply: Plucker slab of %d pixels does not fit", a.pix_per_block);
-    static bool attr_set = false;
-    if (!attr_set) {
-      SEVA_CUDA(cudaFuncSetAttribute(gn_apply_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_set = true;
-    }
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(gn_apply_dense_kernel), 200 * 1024)) return 2;
     gn_apply_dense_kernel<<<grid, threads, smem_d, stream>>>(a);
   } else if (vec8)
     gn_apply_kernel<false, 8, 4><<<grid, threads, smem, stream>>>(a);

@@ -403,11 +403,7 @@ struct TmArgs {
 template <int KT>
 int launch_timemix_mma(const TmArgs& a, cudaStream_t stream) {
   const size_t smem = (size_t)kTmmWarps * KT * kTmmBytes;
-  static bool attr_set = false;
-  if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(timemix_mma_kernel<KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (ensure_dyn_smem(reinterpret_cast<const void*>(timemix_mma_kernel<KT>), (int)smem)) return 2;
   const long long total = (long long)a.B * a.S * a.Hh;
   long long grid = (KT == 1 ? 4ll : 2ll) * sm_count();  // resident blocks per SM, each warp striding over items
   const long long need = (total + kTmmWarps - 1) / kTmmWarps;
@@ -422,12 +418,7 @@ int launch_timemix_mma(const TmArgs& a, cudaStream_t stream) {
 template <int TMAX>
 int launch_timemix(const TmArgs& a, cudaStream_t stream) {
   const size_t smem = sizeof(uint32_t) * kTmWarps * (2 * TMAX * 32 + 32 * 33);
-  static bool attr_set = false;
-  if (!attr_set) {
-    SEVA_CUDA(cudaFuncSetAttribute(timemix_attn_kernel<TMAX>,
-                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (ensure_dyn_smem(reinterpret_cast<const void*>(timemix_attn_kernel<TMAX>), (int)smem)) return 2;
   const long long total = (long long)a.B * a.S * a.Hh;
   const long long grid = (total + kTmWarps - 1) / kTmWarps;
   SEVA_CHECK(grid < (1ll << 31), "seva_timemix_attn: grid too large");

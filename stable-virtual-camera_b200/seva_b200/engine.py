@@ -275,6 +275,14 @@ class Engine:
         self._invariant: set = set()
         self._epoch = None
         self._skip_invariant = False
+        # The plan is static (constant pointers and sizes), so after one eager run per variant (all launches / the
+        # conditioning-only launches skipped) it is captured into a CUDA graph and replayed: one driver call per forward
+        # instead of ~600 ctypes calls, each with its cuTensorMapEncodeTiled (the descriptors are baked into the
+        # captured kernel parameters).  Not used with a frame shard (its collectives go through torch.distributed) or
+        # while per-launch timing is on.  SEVA_CUDA_GRAPH=0 turns it off.
+        self.use_graph = os.environ.get("SEVA_CUDA_GRAPH", "1") != "0" and shard is None
+        self._graphs: dict = {}
+        self._eager_runs: dict = {}
 
         # static inputs
         self.net_in = self.buf("net_in", self.rows_p(0), 64)
@@ -425,7 +433,9 @@ class Engine:
         te = self.P["time_embed"]
         self.add(lib.seva_timestep_embedding, self.t_in.data_ptr(), temb.data_ptr(), N, mc, 10000.0)
         self.gemv(temb, te["w0"], te["b0"], e1, silu_out=True)
-        self.gemv(e1, te["w2"], te["b2"], self.emb)
+        # ``emb`` is consumed only through ``emb_layers = Sequential(SiLU, Linear)`` (layers.py:102-105): the SiLU is
+        # applied once here instead of once per ResBlock and column tile
+        self.gemv(e1, te["w2"], te["b2"], self.emb, silu_out=True)
         # Plucker map resized once per level (layers.py:126-128), channels-last fp32
         self.dense = []
         for l, (H, Wd) in enumerate(self.HW):
@@ -517,7 +527,7 @@ class Engine:
         self.gn(x, l, cin, w["g1"], w["b1"], w["eps1"], h1, silu=True, dense=self.dense[l], dense_w=w["wd"],
                 dense_b=w["bd"])
         emb_out = self.buf(f"rb_emb_{id(m)}", self.N, cout, F32)
-        self.gemv(self.emb, w["we"], w["be"], emb_out, silu_in=True, group="emb")
+        self.gemv(self.emb, w["we"], w["be"], emb_out, group="emb")
         h2 = self.buf(f"rb_h2_{l}", rp, cout)
         self.conv3x3(h1, l, w["w1"], w["cb1"], h2, rowbias=emb_out)
         h3 = self.buf(f"rb_h3_{l}", rp, cout)
@@ -730,19 +740,43 @@ class Engine:
         """Launches of a step whose conditioning is already bound."""
         return self.n_launch - len(self._invariant)
 
+    def _launch_all(self, skip, stream) -> None:
+        for i, (fn, args) in enumerate(self.calls):
+            if i in skip:
+                continue
+            rc = fn(*args, stream)
+            if rc != 0:
+                raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
+
+    def _capture(self, skip):
+        """Record the plan (minus ``skip``) into a CUDA graph.  Nothing is allocated while capturing (every workspace
+        exists already) and the launches only enqueue kernels, so the capture itself does no work: the caller replays."""
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._launch_all(skip, torch.cuda.current_stream().cuda_stream)
+        return g
+
     def run(self, timing: list | None = None) -> None:
         """Launch the plan on the current stream.  With ``timing`` (a list), a CUDA-event pair is recorded around
         every launch and (index, start, end) is appended; read ``self.meta[index]`` for name / algorithmic work."""
+        if torch.cuda.current_device() != self.dev.index:  # pointers, stream and smem opt-ins all belong to self.dev
+            with torch.cuda.device(self.dev):
+                return self.run(timing)
         stream = torch.cuda.current_stream().cuda_stream
         timing = self.timing_sink if timing is None else timing
         skip = self._invariant if self._skip_invariant else ()
         if timing is None:
-            for i, (fn, args) in enumerate(self.calls):
-                if i in skip:
-                    continue
-                rc = fn(*args, stream)
-                if rc != 0:
-                    raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
+            if self.use_graph:
+                variant = bool(self._skip_invariant)
+                g = self._graphs.get(variant)
+                if g is None and self._eager_runs.get(variant, 0) >= 1 and not torch.cuda.is_current_stream_capturing():
+                    g = self._capture(skip)
+                    self._graphs[variant] = g
+                if g is not None:
+                    g.replay()
+                    return
+                self._eager_runs[variant] = self._eager_runs.get(variant, 0) + 1
+            self._launch_all(skip, stream)
             return
         for i, (fn, args) in enumerate(self.calls):
             if i in skip:

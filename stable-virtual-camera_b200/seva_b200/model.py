@@ -270,7 +270,10 @@ class Seva(nn.Module):
         assert y.ndim == 3
         n, cin, h, w = x.shape
         assert cin == self.params.in_channels and n % num_frames == 0
-        with torch.autocast("cuda", enabled=False):
+        dev = next(self.parameters()).device
+        if x.device != dev:
+            raise SevaB200Error(f"Seva.forward: input on {x.device}, parameters on {dev}")
+        with torch.autocast("cuda", enabled=False), torch.cuda.device(dev):
             eng = self.engine(n, num_frames, h, w, y.shape[1])
             sh = eng.shard
             if sh is None:

@@ -267,7 +267,8 @@ def multiview_scale(c2w: torch.Tensor, K: torch.Tensor, input_mask: torch.Tensor
     T = c2w.shape[0]
     c2w4 = c2w.contiguous()
     assert c2w4.shape[-2:] == (4, 4), "c2w must be [T,4,4]"
-    mask_u8 = input_mask.to(torch.uint8).contiguous()
+    mask_u8 = input_mask.to(device=c2w.device, dtype=torch.uint8).contiguous()  # the reference accepts a CPU mask
+    K = K.to(c2w.device)
     if isinstance(scale, torch.Tensor):
         sc = scale.reshape(-1).to(device=c2w.device, dtype=torch.float32).contiguous()
         is_vec = int(sc.numel() > 1)
@@ -299,8 +300,18 @@ def sigma_quantize(sigma: torch.Tensor, table: torch.Tensor):
     return idx, sq, c_in, c_out
 
 
+def _req_on(dev, dtype, **tensors) -> None:
+    """Every tensor a kernel dereferences must live on the launch device with the dtype the kernel assumes."""
+    for name, t in tensors.items():
+        if t is None:
+            continue
+        _req(t, dtype, name)
+        if t.device != dev:
+            raise _lib.SevaB200Error(f"{name} is on {t.device}, expected {dev}")
+
+
 def add_noise(x: torch.Tensor, eps: torch.Tensor, sigma: torch.Tensor, sigma_hat: torch.Tensor) -> torch.Tensor:
-    _req(x, torch.float32, "x"), _req(eps, torch.float32, "eps")
+    _req_on(x.device, torch.float32, x=x, eps=eps, sigma=sigma, sigma_hat=sigma_hat)
     x, eps = x.contiguous(), eps.contiguous()
     out = torch.empty_like(x)
     T = x.shape[0]
@@ -311,12 +322,23 @@ def add_noise(x: torch.Tensor, eps: torch.Tensor, sigma: torch.Tensor, sigma_hat
 
 
 def denoise_prepare(x, replace, concat, c_in, net_in, blended_out, N, x_frames, h, w) -> None:
+    _req_on(net_in.device, torch.float32, x=x, replace=replace, concat=concat, c_in=c_in, blended_out=blended_out)
+    if tuple(concat.shape) != (N, 7, h, w) or (replace is not None and tuple(replace.shape) != (N, 5, h, w)) \
+            or tuple(x.shape) != (x_frames, 4, h, w) or c_in.numel() != N or net_in.shape[1] < 16:
+        raise _lib.SevaB200Error("seva_denoise_prepare: expected x [x_frames,4,h,w], replace [N,5,h,w], concat [N,7,h,w], "
+                                 f"c_in [N]; got {tuple(x.shape)}, {None if replace is None else tuple(replace.shape)}, "
+                                 f"{tuple(concat.shape)}, {tuple(c_in.shape)}")
+    if not (x.is_contiguous() and concat.is_contiguous() and (replace is None or replace.is_contiguous())):
+        raise _lib.SevaB200Error("seva_denoise_prepare: inputs must be contiguous")
     check(_lib.load().seva_denoise_prepare(x.data_ptr(), _p(replace), concat.data_ptr(), c_in.data_ptr(),
                                            net_in.data_ptr(), net_in.stride(0), blended_out.data_ptr(), N,
                                            x_frames, h, w, _stream()), "seva_denoise_prepare")
 
 
 def denoise_finish(eps, blended, c_out, out, N, h, w) -> None:
+    _req_on(eps.device, torch.float32, eps=eps, blended=blended, c_out=c_out, out=out)
+    if eps.shape[1] < 4 or tuple(blended.shape) != (N, 4, h, w) or tuple(out.shape) != (N, 4, h, w) or c_out.numel() != N:
+        raise _lib.SevaB200Error("seva_denoise_finish: expected eps [N*(h+2)*(w+2), >=4], blended / out [N,4,h,w], c_out [N]")
     check(_lib.load().seva_denoise_finish(eps.data_ptr(), eps.stride(0), blended.data_ptr(), c_out.data_ptr(),
                                           out.data_ptr(), N, h, w, _stream()), "seva_denoise_finish")
 
@@ -325,10 +347,11 @@ def cfg_euler_step(x: torch.Tensor, denoised: torch.Tensor, scale: torch.Tensor,
                    sigma_next: torch.Tensor, out: torch.Tensor | None = None,
                    denoised_out: torch.Tensor | None = None) -> torch.Tensor:
     """x [T,...] fp32, denoised [2T,...] (uncond first), scale/sigma_hat/sigma_next [T] -> x_next."""
-    _req(x, torch.float32, "x"), _req(denoised, torch.float32, "denoised")
+    _req_on(x.device, torch.float32, x=x, denoised=denoised, scale=scale, sigma_hat=sigma_hat, sigma_next=sigma_next,
+            out=out, denoised_out=denoised_out)
     x, denoised = x.contiguous(), denoised.contiguous()
     T = x.shape[0]
-    assert denoised.shape[0] == 2 * T
+    assert denoised.shape[0] == 2 * T and scale.numel() == T and sigma_hat.numel() == T and sigma_next.numel() == T
     if out is None:
         out = torch.empty_like(x)
     check(_lib.load().seva_cfg_euler_step(x.data_ptr(), denoised.data_ptr(), scale.data_ptr(),

@@ -116,8 +116,7 @@ class DiscreteDenoiser(object):
 
     def __call__(self, network: nn.Module, input: torch.Tensor, sigma: torch.Tensor, cond: dict,
                  **additional_model_inputs) -> torch.Tensor:
-        if input.is_cuda and self.sigmas.is_cuda and _is_fused_network(network) and input.ndim == 4 \
-                and input.shape[1] == 4 and "concat" in cond:
+        if self._fusable(network, input, sigma, cond):
             return self._call_fused(network, input, sigma, cond, **additional_model_inputs)
         sigma = self.idx_to_sigma(self.sigma_to_idx(sigma))
         sigma_shape = sigma.shape
@@ -129,12 +128,36 @@ class DiscreteDenoiser(object):
             input = input * (1 - mask) + x * mask
         return network(input * c_in, c_noise, cond, **additional_model_inputs) * c_out + input * c_skip
 
+    def _fusable(self, network, input, sigma, cond) -> bool:
+        """The fused kernels hard-code the released model's boundary: 4 latent + 7 concat (mask, Plucker) input
+        channels, a 5-channel ``replace`` (latent + mask), 4 output channels, everything resident on the model's
+        GPU.  Anything else takes the generic branch below, which states the reference's arithmetic in PyTorch and
+        raises the reference's shape errors."""
+        if not (input.is_cuda and self.sigmas.is_cuda and sigma.is_cuda and _is_fused_network(network)):
+            return False
+        module = getattr(network, "_orig_mod", network).module
+        p = module.params
+        if next(module.parameters()).device != input.device or self.sigmas.device != input.device:
+            return False
+        if not (input.ndim == 4 and input.shape[1] == 4 and p.in_channels == 11 and p.out_channels == 4):
+            return False
+        cc, rep = cond.get("concat"), cond.get("replace")
+        same = lambda t: isinstance(t, torch.Tensor) and t.device == input.device
+        if not (same(cc) and cc.ndim == 4 and cc.shape[1] == 7 and cc.shape[0] == input.shape[0]
+                and cc.shape[2:] == input.shape[2:]):
+            return False
+        if rep is not None and not (same(rep) and rep.ndim == 4 and rep.shape[1] == 5 and rep.shape[0] == input.shape[0]
+                                    and rep.shape[2:] == input.shape[2:]):
+            return False
+        return same(cond.get("crossattn")) and same(cond.get("dense_vector")) and cond["crossattn"].ndim == 3 \
+            and cond["dense_vector"].shape[1] == p.dense_in_channels and sigma.numel() == input.shape[0]
+
     def _call_fused(self, network, input, sigma, cond, num_frames=None, **extra):
         """Same arithmetic as above with the elementwise work fused around the network plan."""
         module = getattr(network, "_orig_mod", network).module
         num_frames = num_frames or module.params.num_frames
         n, _, h, w = input.shape
-        with torch.autocast("cuda", enabled=False):
+        with torch.autocast("cuda", enabled=False), torch.cuda.device(input.device):
             idx, _, c_in, c_out = ops.sigma_quantize(sigma.float().reshape(-1), self.sigmas)
             replace = cond.pop("replace", None)  # the reference pops it from the per-step dict (sampling.py:147)
             eng = module.engine(n, num_frames, h, w, cond["crossattn"].shape[1])
