@@ -133,6 +133,73 @@ def make_host_inputs(T, h, w, seed):
                 c2w=pin(inp["c2w"]), K=pin(inp["K"]), mask=pin(inp["mask"]))
 
 
+def strong_scaling_extra(args, model, dev, world, rank):
+    """Extra key of the N > 1 line (the headline `value` stays chunk data-parallel, the metric's workload): ONE T-frame
+    chunk over all N GPUs -- CFG halves on rank pairs x frame sequence-parallel over N/2 (BASELINE configs[3]) -- so
+    that the driver's scaling file also records the strong-scaling curve and the K/V-exchange share.  Collective: every
+    rank must call it.  Device time (CUDA events), max over ranks."""
+    import torch.distributed as dist
+
+    from seva_b200 import dist as D
+    from seva_b200 import sampling as S
+    from seva_b200.engine import _FrameGather, _RingAttention, _RingStart, _SpaceExchange
+
+    T, h, w = args.T, args.size, args.size
+    topo = D.Topology(world, rank, cfg=2, sp=world // 2)
+    groups = D.build_groups(topo)
+    if groups["frames"] is not None:
+        model.module.set_frame_group(groups["frames"])
+    guider = D.CFGSplit(S.MultiviewCFG(1.2), groups["cfg"], half=topo.half)
+    torch.manual_seed(1234)  # replicated sampler state: identical noise on every rank
+    host = make_host_inputs(T, h, w, seed=1)
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device=dev)
+    sampler = S.EulerEDMSampler(disc, guider, num_steps=50, s_churn=0.0, s_tmin=0.0, s_tmax=999.0, s_noise=1.0,
+                                verbose=False, device=dev)
+    sigmas = disc(50, device=dev)
+    nb = lambda t: t.to(dev)
+    x = nb(host["x0"]) * 84.9222
+    c, uc = {k: nb(v) for k, v in host["c"].items()}, {k: nb(v) for k, v in host["uc"].items()}
+    kw = dict(c2w=nb(host["c2w"]), K=nb(host["K"]), input_frame_mask=nb(host["mask"]))
+    den_fn = lambda i, s_, cc: denoiser(model, i, s_, cc, num_frames=T)
+    ones = x.new_ones([T])
+    step = lambda i: sampler.sampler_step(ones * sigmas[i % 50], ones * sigmas[i % 50 + 1], den_fn, x, 2.0, c, uc, 0.0, **kw)
+    steps = max(3, min(args.steps, 10))
+    with torch.inference_mode(), torch.autocast("cuda"):
+        for i in range(3):
+            step(i)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            out = step(i)
+        e1.record()
+        dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # exchange share: the same steps once more with an event pair around every plan entry (rank 0's view)
+        eng = next(iter(model.module._engines.values()))
+        timing: list = []
+        eng.timing_sink = timing
+        for i in range(2):
+            step(i)
+        torch.cuda.synchronize()
+        eng.timing_sink = None
+    xch = sum(a.elapsed_time(b) for idx, a, b in timing
+              if isinstance(eng.calls[idx][0], (_FrameGather, _SpaceExchange, _RingStart))) / 2
+    ring = sum(a.elapsed_time(b) for idx, a, b in timing if isinstance(eng.calls[idx][0], _RingAttention)) / 2
+    total = sum(a.elapsed_time(b) for idx, a, b in timing) / 2
+    assert torch.isfinite(out).all()
+    model.module.set_frame_group(None)
+    ms = t.item() / steps
+    return {"value": round(T / (ms / 1e3), 3), "unit": "frame-steps/s", "ms_per_step": round(ms, 3), "steps": steps,
+            "scaling": "strong", "parallelism": f"one chunk over {world} GPUs: cfg2 x frames{world // 2}",
+            "blocking_exchange_ms_per_step": round(xch, 3), "attn3d_with_overlapped_exchange_ms_per_step": round(ring, 3),
+            "plan_ms_per_step": round(total, 3), "ring_mode": os.environ.get("SEVA_RING", "ring")}
+
+
 def run_ours(args):
     from seva_b200 import sampling as S
 
@@ -293,6 +360,16 @@ def run_ours(args):
                     frac=round(ach / peaks["hbm"], 4), traffic=traffic.get(tname), peak_source=peaks["source"],
                     launches=ta["n"], avg_launch_ms=round(ta["ms"] / ta["n"], 4))
 
+    n_launch_step = eng.n_launch_step
+    strong = None
+    if world > 1 and world % 2 == 0 and args.parallel == "chunks" and not args.no_strong:
+        del eng
+        model.module.invalidate()
+        torch.cuda.empty_cache()
+        try:
+            strong = strong_scaling_extra(args, model, dev, world, rank)
+        except Exception as e:  # never take the headline line down
+            strong = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     if rank != 0:
         return
     steps = args.steps
@@ -300,7 +377,6 @@ def run_ours(args):
     e2e_v = chunks_world * T * steps / (ms_e2e / 1e3)
     tf_step = REF_TFLOP_PER_STEP.get(T)
     lib = None
-    n_launch_step = eng.n_launch_step
     if world == 1 and not args.no_gpu_baseline:
         model.module.invalidate()  # return our workspaces before the reference modules allocate theirs
         del eng
@@ -329,6 +405,8 @@ def run_ours(args):
         line["cpu_baseline"] = cpu
     if lib is not None:
         line["gpu_library_baseline"] = lib
+    if strong is not None:
+        line["strong_cfg_frames"] = strong
     print(json.dumps(line))
 
 
@@ -603,6 +681,7 @@ if __name__ == "__main__":
     ap.add_argument("--workload", default="step", choices=["step", "scene"],
                     help="step: one Euler-EDM step of configs[1] (the driver's contract); scene: configs[2] end to end")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the extra strong-scaling (cfg2 x frames) leg")
     ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the eager-PyTorch reference-on-GPU leg")
     ap.add_argument("--cpu-budget", type=float, default=float(os.environ.get("SEVA_CPU_BUDGET_S", 300)),
                     help="seconds the CPU reference leg may spend (it always times at least one full step)")

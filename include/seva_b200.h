@@ -72,8 +72,24 @@ typedef struct SevaGemm {
   int32_t reverse;     /* 1: process (and write) row tiles from the last to the first.  L2-aware traversal:
                         * a consumer that walks a tensor in the OPPOSITE order to the kernel that last touched
                         * it finds the most recent ~100 MB still in the 126 MB L2.  Results are identical.   */
+  /* ---- statistics of the OUTPUT for the normalisation that consumes it (coalesced bf16 epilogue only).  They replace
+   *      a separate read pass over the tensor: GroupNorm32 at layers.py:99,110, transformer.py:186, model.py:171;
+   *      nn.LayerNorm at transformer.py:102-104,124,141-143.  All NULL / 0 = off. */
+  float* gn_partial;   /* fp32 [images][gn_slots][N][2]: per-channel (sum, sum of squares) of every 32-row block of M
+                        * space, slot = block - first block of the image; folded by seva_groupnorm_finalize          */
+  int32_t gn_rpi;      /* rows of M space per image: H*W (compact / out_map = 1) or (H+2)*(W+2) (zero-bordered)        */
+  int32_t gn_slots;    /* (gn_rpi + 31) / 32 + 1                                                                      */
+  float* ln_rowstats;  /* fp32 [seva_gemm_ln_slots(N, bn)][M][2]: per-row (sum, sum of squares) over each column share */
+  /* ---- LayerNorm folded INTO this GEMM (nn.LayerNorm -> nn.Linear, transformer.py:107-110,150-153): A is the
+   *      un-normalised input, W is pre-multiplied by gamma along K, `bias` holds beta . W^T + b, and
+   *      out[m, n] = rstd[m] * (acc[m, n] - mean[m] * ln_colsum[n]) + bias[n]  (before GEGLU / residual).             */
+  const float* ln_in_stats;  /* the ln_rowstats buffer the producer of A wrote: [ln_in_slots][M][2], or NULL          */
+  int32_t ln_in_slots;
+  float ln_eps;
+  const float* ln_colsum;    /* fp32 [N]: sum over k of the (bf16, gamma-scaled) W[n, k]                              */
 } SevaGemm;
 int seva_gemm_bf16(const SevaGemm* g, void* stream);
+int seva_gemm_ln_slots(int32_t N, int32_t bn);
 /* N tile seva_gemm_bf16 will use for (N, geglu) when g->bn == 0 (weights for geglu are packed against it). */
 int seva_gemm_pick_bn(int32_t N, int32_t geglu);
 
@@ -83,6 +99,16 @@ int seva_gemm_pick_bn(int32_t N, int32_t geglu);
 int seva_attn_fwd(const void* q, const void* k, const void* v, void* o, int32_t B, int32_t Hh,
                   int32_t Lq, int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo,
                   int64_t bsq, int64_t bsk, int64_t bsv, int64_t bso, float scale, void* stream);
+/* Keys split over several launches (frame sequence-parallel ranks attend to each peer's K/V block as it arrives, SURVEY
+ * 8e "ring"): seva_attn_partial computes the attention of q over ONE key block and writes the normalised fp32 result
+ * o_f32 [B, Lq, Hh*64] plus the base-2 log-sum-exp lse [B, Hh, Lq] of its scores; seva_attn_merge combines P such
+ * results (partials [P, B, Lq, Hh*64], lse [P, B, Hh, Lq], both contiguous) into the bf16 output of seva_attn_fwd
+ * over the union of the key blocks (online-softmax merge). */
+int seva_attn_partial(const void* q, const void* k, const void* v, float* o_f32, float* lse, int32_t B, int32_t Hh,
+                      int32_t Lq, int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t bsq, int64_t bsk,
+                      int64_t bsv, float scale, void* stream);
+int seva_attn_merge(const float* partials, const float* lse, void* out, int32_t P, int32_t B, int32_t Hh, int32_t Lq,
+                    int64_t ldo, int64_t bso, void* stream);
 /* Attention over the frame axis: tokens are rows (b*T + t)*S + s of qkv [B*T*S, 3*C] (q | k | v, C = Hh*64);
  * for every (b, s, h) softmax over t' of the T frames.  out [B*T*S, C] (row stride ldo). */
 int seva_timemix_attn(const void* qkv, void* out, int32_t B, int32_t T, int32_t S, int32_t Hh,
@@ -117,7 +143,17 @@ typedef struct SevaGNApply {
   const float* dense_w;           /* fp32 [2C, 6] (scale rows first, then shift rows)                     */
   const float* dense_b;           /* fp32 [2C]                                                            */
   int32_t reverse;                /* 1: walk images / pixels from the last to the first (see SevaGemm.reverse) */
+  const float* gstats;            /* optional fp32 [Nimg, groups, 2] (mean, rstd) from seva_groupnorm_finalize; when set,
+                                   * `sums` is not read (may be NULL)                                           */
 } SevaGNApply;
+/* GroupNorm statistics WITHOUT a pass over the tensor: the GEMM that produced it wrote per-32-row-block partials
+ * (SevaGemm.gn_partial, seva_groupnorm_partial_floats(Nimg, gn_rpi, N) floats); this folds them, in slot order and in
+ * fp64, into gstats[Nimg, groups, 2] = (mean, 1/sqrt(var + eps)).  Two sources side by side along the channel axis
+ * (C0 then C1 channels; the decoder's virtual skip concat, model.py:207) may have different row spaces (rpi0 / rpi1);
+ * part1 = NULL, C1 = 0 for one source.  `pixels` = H*W (zero-border rows contribute zeros and are not counted). */
+int seva_groupnorm_partial_floats(int32_t Nimg, int32_t rpi, int32_t C);
+int seva_groupnorm_finalize(const float* part0, int32_t C0, int32_t rpi0, const float* part1, int32_t C1, int32_t rpi1,
+                            int32_t Nimg, int32_t groups, int32_t pixels, float eps, float* gstats, void* stream);
 int seva_groupnorm_apply(const SevaGNApply* p, void* stream);
 /* y[m, :] = LayerNorm(x[m, :]) * gamma + beta, eps inside sqrt; bf16 in/out, fp32 statistics. */
 int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, const float* gamma,

@@ -44,6 +44,9 @@ struct AttnArgs {
   __nv_bfloat16* o;
   long long ldo, bso;
   float scale_log2;
+  // partial mode (keys split over several launches, seva_attn_partial): o is fp32 (ldo / bso in floats) and the
+  // base-2 log-sum-exp of every (batch, head, query) over THIS launch's keys is written to lse
+  float* lse;
 };
 
 // ---- packed fp32x2 helpers (FFMA2 / FADD2 on sm_100) ------------------------------------------
@@ -388,12 +391,23 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const int qrow = q0 + i * 128 + row;
     const float inv_l = 1.0f / l_run;
     __nv_bfloat16* optr = a.o + (long long)b * a.bso + (long long)qrow * a.ldo + head * 64;
+    if (a.lse != nullptr && qrow < a.Lq)
+      a.lse[((long long)b * a.Hh + head) * a.Lq + qrow] = m_run + log2f(l_run);
 #pragma unroll 1
     for (int c = 0; c < 2; ++c) {
       uint32_t v[32];
       tmem_ld32(tO + c * 32, v);
       tmem_wait_ld();
-      if (qrow < a.Lq) {
+      if (a.lse != nullptr) {  // fp32 partial result
+        if (qrow < a.Lq) {
+          float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(a.o) + (long long)b * a.bso +
+                                                 (long long)qrow * a.ldo + head * 64 + c * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            o4[q] = make_float4(__uint_as_float(v[4 * q]) * inv_l, __uint_as_float(v[4 * q + 1]) * inv_l,
+                                __uint_as_float(v[4 * q + 2]) * inv_l, __uint_as_float(v[4 * q + 3]) * inv_l);
+        }
+      } else if (qrow < a.Lq) {
         uint4* o4 = reinterpret_cast<uint4*>(optr + c * 32);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -416,13 +430,86 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   }
 }
 
+// Merge of P partial attention results over disjoint key sets (frame sequence-parallel ranks: one launch per
+// rank's K/V block, started as the blocks arrive): out = sum_p w_p O_p, w_p = 2^(lse_p - max) / sum_p 2^(lse_p - max).
+// 16 threads per (batch, query, head): 4 columns each.
+__global__ void __launch_bounds__(256)
+attn_merge_kernel(const float* __restrict__ part, const float* __restrict__ lse, __nv_bfloat16* __restrict__ out,
+                  int P, int B, int Hh, int Lq, long long part_stride, long long lse_stride, long long ldo, long long bso) {
+  const long long gid = (long long)blockIdx.x * 16 + (threadIdx.x >> 4);
+  const int d4 = threadIdx.x & 15;
+  const long long total = (long long)B * Lq * Hh;
+  if (gid >= total) return;
+  const int h = (int)(gid % Hh);
+  const long long br = gid / Hh;
+  const int row = (int)(br % Lq);
+  const int b = (int)(br / Lq);
+  const long long lidx = ((long long)b * Hh + h) * Lq + row;
+  float mx = -INFINITY;
+  for (int p = 0; p < P; ++p) mx = fmaxf(mx, __ldg(lse + p * lse_stride + lidx));
+  float wsum = 0.f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const long long C = (long long)Hh * 64;
+  const long long oidx = ((long long)b * Lq + row) * C + h * 64 + d4 * 4;
+  for (int p = 0; p < P; ++p) {
+    const float w = exp2f(__ldg(lse + p * lse_stride + lidx) - mx);
+    const float4 v = __ldg(reinterpret_cast<const float4*>(part + p * part_stride + oidx));
+    wsum += w;
+    acc.x = fmaf(w, v.x, acc.x);
+    acc.y = fmaf(w, v.y, acc.y);
+    acc.z = fmaf(w, v.z, acc.z);
+    acc.w = fmaf(w, v.w, acc.w);
+  }
+  const float inv = 1.0f / wsum;
+  uint2 o;
+  o.x = pack_bf16x2(acc.x * inv, acc.y * inv);
+  o.y = pack_bf16x2(acc.z * inv, acc.w * inv);
+  *reinterpret_cast<uint2*>(out + (long long)b * bso + (long long)row * ldo + h * 64 + d4 * 4) = o;
+}
+
 }  // namespace
 }  // namespace seva
+
+static int attn_launch(const void* q, const void* k, const void* v, void* o, float* lse, int32_t B, int32_t Hh, int32_t Lq,
+                       int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t bsq, int64_t bsk, int64_t bsv,
+                       int64_t bso, float scale, void* stream_v);
 
 extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* o, int32_t B,
                              int32_t Hh, int32_t Lq, int32_t Lk, int64_t ldq, int64_t ldk,
                              int64_t ldv, int64_t ldo, int64_t bsq, int64_t bsk, int64_t bsv,
                              int64_t bso, float scale, void* stream_v) {
+  return attn_launch(q, k, v, o, nullptr, B, Hh, Lq, Lk, ldq, ldk, ldv, ldo, bsq, bsk, bsv, bso, scale, stream_v);
+}
+
+extern "C" int seva_attn_partial(const void* q, const void* k, const void* v, float* o_f32, float* lse, int32_t B,
+                                 int32_t Hh, int32_t Lq, int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t bsq,
+                                 int64_t bsk, int64_t bsv, float scale, void* stream_v) {
+  using namespace seva;
+  SEVA_CHECK(lse != nullptr, "seva_attn_partial: lse must not be null");
+  const int64_t C = (int64_t)Hh * 64;
+  return attn_launch(q, k, v, o_f32, lse, B, Hh, Lq, Lk, ldq, ldk, ldv, C, bsq, bsk, bsv, (int64_t)Lq * C, scale, stream_v);
+}
+
+extern "C" int seva_attn_merge(const float* partials, const float* lse, void* out, int32_t P, int32_t B, int32_t Hh,
+                               int32_t Lq, int64_t ldo, int64_t bso, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(partials && lse && out && P > 0 && B > 0 && Hh > 0 && Lq > 0, "seva_attn_merge: bad arguments");
+  SEVA_CHECK((ldo % 4) == 0 && (bso % 4) == 0 && ((uintptr_t)out & 7) == 0 && ((uintptr_t)partials & 15) == 0,
+             "seva_attn_merge: alignment");
+  const long long total = (long long)B * Lq * Hh;
+  const long long blocks = (total + 15) / 16;
+  SEVA_CHECK(blocks < (1ll << 31), "seva_attn_merge: too many rows");
+  attn_merge_kernel<<<(unsigned)blocks, 256, 0, stream>>>(partials, lse, reinterpret_cast<__nv_bfloat16*>(out), P, B, Hh, Lq,
+                                                          (long long)B * Lq * Hh * 64, (long long)B * Hh * Lq, ldo, bso);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int attn_launch(const void* q, const void* k, const void* v, void* o, float* lse, int32_t B, int32_t Hh, int32_t Lq,
+                       int32_t Lk, int64_t ldq, int64_t ldk, int64_t ldv, int64_t ldo, int64_t bsq, int64_t bsk, int64_t bsv,
+                       int64_t bso, float scale, void* stream_v) {
   using namespace seva;
   if (check_device()) return 3;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
@@ -462,6 +549,7 @@ extern "C" int seva_attn_fwd(const void* q, const void* k, const void* v, void* 
   a.ldo = ldo;
   a.bso = bso;
   a.scale_log2 = scale * 1.4426950408889634f;
+  a.lse = lse;
   dim3 grid((Lq + 255) / 256, Hh, B);
 #define SEVA_ATTN_LAUNCH(E, P)                                                                      \
   {                                                                                                 \

@@ -169,9 +169,11 @@ __device__ __forceinline__ uint32_t mapa_cluster(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Default semantics (release at CTA scope): the callers order their tcgen05 traffic with tcgen05.fence and hand over
+// no generic-proxy data, and `.release.cluster` compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive (ncu r2c:
+// 8 % of the pair kernel's epilogue stall samples sat on it).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr)
-               : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load issued by either CTA of a pair; `bar_cluster` may address the peer CTA's mbarrier.
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar_cluster,

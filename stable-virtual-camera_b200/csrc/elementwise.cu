@@ -444,9 +444,9 @@ timestep_embedding_kernel(const long long* __restrict__ t, float* __restrict__ o
 // Per pass (kGwRows rows x kGwCols columns): K/256 trips of 4 + 16 loads and 256 FMAs per lane, then a butterfly
 // reduction.  (The previous kernel walked one weight row per THREAD with the x rows in shared memory: a serial chain
 // of 160 dependent 16-byte loads per column -- 456 us for the 22 emb_layers at M = 42 against ~60 MB of weights.)
-// Grouped form: blockIdx.y selects one of `count` independent problems (descriptor table in device memory), so the
+// Grouped form: blockIdx.z selects one of `count` independent problems (descriptor table in device memory), so the
 // ~90 tiny per-step GEMVs are 3 launches.
-constexpr int kGwCols = 4;
+constexpr int kGwCols = 4;      // columns per warp in the grouped kernel (many problems fill the GPU)
 constexpr int kGwRows = 8;
 constexpr int kGwWarps = 8;   // 32 columns per block
 
@@ -461,7 +461,9 @@ __device__ __forceinline__ void gemv_warp_tile(const float* __restrict__ x, cons
   const __nv_bfloat16* wrow[kGwCols];
 #pragma unroll
   for (int c = 0; c < kGwCols; ++c) wrow[c] = W + (long long)min(n0 + c, N - 1) * K;
-  for (int m0 = 0; m0 < M; m0 += kGwRows) {
+  {
+    const int m0 = (int)blockIdx.y * kGwRows;   // one pass of kGwRows rows per block row (weights re-read through L2)
+    if (m0 >= M) return;
     float acc[kGwRows][kGwCols];
 #pragma unroll
     for (int r = 0; r < kGwRows; ++r)
@@ -525,7 +527,7 @@ gemv_rows_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ 
 
 __global__ void __launch_bounds__(kGwWarps * 32)
 gemv_grouped_kernel(const SevaGemvProblem* __restrict__ probs) {
-  const SevaGemvProblem p = probs[blockIdx.y];
+  const SevaGemvProblem p = probs[blockIdx.z];
   gemv_warp_tile(p.x, reinterpret_cast<const __nv_bfloat16*>(p.W), p.bias, p.out, p.M, p.N, p.K, p.silu_in,
                  p.silu_out);
 }
@@ -729,7 +731,7 @@ extern "C" int seva_gemv_rows(const float* x, const void* W, const float* bias, 
   SEVA_CHECK(M > 0 && N > 0 && K > 0 && (K % 8) == 0, "seva_gemv_rows: need K %% 8 == 0");
   SEVA_CHECK((((uintptr_t)x | (uintptr_t)W) & 15) == 0, "seva_gemv_rows: x and W must be 16-byte aligned");
   const int cols_per_block = kGwWarps * kGwCols;
-  gemv_rows_kernel<<<(N + cols_per_block - 1) / cols_per_block, kGwWarps * 32, 0, stream>>>(
+  gemv_rows_kernel<<<dim3((N + cols_per_block - 1) / cols_per_block, (M + kGwRows - 1) / kGwRows), kGwWarps * 32, 0, stream>>>(
       x, reinterpret_cast<const __nv_bfloat16*>(W), bias, out, M, N, K, silu_in, silu_out);
   SEVA_CUDA(cudaGetLastError());
   return 0;
@@ -742,7 +744,7 @@ extern "C" int seva_gemv_grouped(const SevaGemvProblem* problems_dev, int32_t co
   SEVA_CHECK(problems_dev && count > 0 && max_M > 0 && max_N > 0 && max_K > 0, "seva_gemv_grouped: bad arguments");
   SEVA_CHECK((max_K % 8) == 0 && count <= 65535, "seva_gemv_grouped: K must be a multiple of 8, count <= 65535");
   const int cols_per_block = kGwWarps * kGwCols;
-  dim3 grid((max_N + cols_per_block - 1) / cols_per_block, count);
+  dim3 grid((max_N + cols_per_block - 1) / cols_per_block, (max_M + kGwRows - 1) / kGwRows, count);
   gemv_grouped_kernel<<<grid, kGwWarps * 32, 0, stream>>>(problems_dev);
   SEVA_CUDA(cudaGetLastError());
   return 0;

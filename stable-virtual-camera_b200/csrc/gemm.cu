@@ -36,7 +36,8 @@ constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 constexpr int kSmemMax = 232448;         // 227 KB: the most dynamic smem one CTA can opt in to
 constexpr int kCtrlBytes = 1024;         // barriers + tmem pointer live in the first KB
 constexpr int kPatchBytes = 4096;        // per-epilogue-warp transpose patch: 32 rows x 128 B
-constexpr int kBiasSlotBytes = 512;      // per-epilogue-warp column constants of the current tile (128 fp32)
+constexpr int kBiasSlotBytes = 1024;     // per-epilogue-warp column constants of the current tile: 128 fp32 bias (+ 128 fp32 LayerNorm column sums)
+constexpr int kMaxLnSlots = 10;          // row-statistic partials per row a LayerNorm-folding GEMM can read
 constexpr int kMaxStages = 8;
 
 // Developer knobs (skip TMA loads / barrier waits / epilogue stores for pipeline A/B measurements) exist only in
@@ -62,6 +63,15 @@ struct GemmArgs {
   int reverse;  // 1: walk the tile list backwards (L2-aware traversal, see seva_b200.h)
   int fast;  // 1: bf16 output, N % 32 == 0 and 16-byte aligned pointers/strides -> coalesced epilogue
   int wstat;  // 1: weight-stationary walk (opt-in): the CTA's N tile of W stays in smem for all of its M tiles
+  // ---- statistics of the OUTPUT, for the normalisation that consumes it (coalesced bf16 epilogue only) ----
+  float* gn_part;      // GroupNorm: [image][slot][N][2] partial (sum, sum of squares) per 32-row block, or null
+  int gn_rpi, gn_slots;
+  float2* ln_rows;     // LayerNorm: [slot][M] per-row partial (sum, sum of squares), slot = n_tile * kParts + part
+  // ---- LayerNorm folded into this GEMM: A is the un-normalised input, W is pre-scaled by gamma ----
+  const float2* ln_in;  // [ln_slots][M] row partials written by the producer of A, or null
+  int ln_slots;
+  float ln_eps, ln_inv_c;
+  const float* ln_colsum;  // fp32 [N]: sum_k W'[n, k]  (bias holds beta . W + b)
 };
 
 // ---- GEGLU: x * gelu(g), exact (erf) GELU --------------------------------------------------------------
@@ -83,6 +93,11 @@ __device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigne
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b) {
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 __device__ __forceinline__ float lo2(unsigned long long v) { return __uint_as_float((uint32_t)v); }
 __device__ __forceinline__ float hi2(unsigned long long v) { return __uint_as_float((uint32_t)(v >> 32)); }
 
@@ -97,11 +112,21 @@ __device__ __forceinline__ void geglu2(float& x0, float& x1, float g0, float g1)
   unsigned long long p = fma2(pk2(kC2, kC2), g2, pk2(kC1, kC1));
   p = fma2(p, g2, pk2(kC0, kC0));
   const unsigned long long u = mul2(g, p);
-  const float e0 = fast_exp2(lo2(u)), e1 = fast_exp2(hi2(u));  // exp(-2 g p)
+#ifdef SEVA_GEGLU_TANH
+  // sigmoid(2 y) = 0.5 + 0.5 tanh(y), y = g p(g^2) = u / (-2 log2 e): ONE MUFU op per element instead of two
+  // (tanh.approx: |error| <= 2^-11, i.e. up to 2.4e-4 on Phi -- measurably noisier than the ex2 + rcp form on strongly
+  // negative gates, which is why this is an A/B build and not the default)
+  constexpr float kS = -0.34657359027997264f;  // -ln(2) / 2
+  const unsigned long long y = mul2(u, pk2(kS, kS));
+  const unsigned long long h = fma2(pk2(fast_tanh(lo2(y)), fast_tanh(hi2(y))), pk2(0.5f, 0.5f), pk2(0.5f, 0.5f));
+  const unsigned long long o = mul2(mul2(pk2(x0, x1), g), h);
+#else
+  const unsigned long long e1p = add2(pk2(fast_exp2(lo2(u)), fast_exp2(hi2(u))), pk2(1.0f, 1.0f));  // 1 + exp(-2 g p)
   float r0, r1;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(e0 + 1.0f));
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(e1 + 1.0f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(lo2(e1p)));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r1) : "f"(hi2(e1p)));
   const unsigned long long o = mul2(mul2(pk2(x0, x1), g), pk2(r0, r1));
+#endif
   x0 = lo2(o);
   x1 = hi2(o);
 }
@@ -161,13 +186,65 @@ __device__ __forceinline__ void finish_store32(const GemmArgs& a, const RowInfo&
   }
 }
 
+// ---- statistics of the output tile, taken in the transposed view of the store functions -------------------------
+// Lane (r = lane >> 2, p = lane & 3) holds the final values of tile rows 8 i + r (i < 4), columns [8 p, 8 p + 8) of the
+// current 32-column chunk.
+//   GroupNorm: per-channel sum / sum of squares over the warp's 32 rows, split by image when the block straddles an
+//     image boundary, written (no atomics: one writer per element, so the result is deterministic) to
+//     gn_part[image][slot][column][2] with slot = (index of the 32-row block in M space) - (first block of the image);
+//     seva_groupnorm_finalize folds the slots.  Zero-border rows hold zeros and add nothing.
+//   LayerNorm (residual path only; the plain path sums in the row-per-thread view): running per-row sums over the
+//     lane's 8 columns, folded over p at the end of the tile.
+struct EpiStats {
+  float* gn_part;
+  int gn_ld, gn_slots, gn_rpi;
+  int blk, img_lo, img_hi;
+  int timg[4];
+  bool rows_on;
+  float rs[4], rq[4];
+};
+
+__device__ __forceinline__ void col_stats(const EpiStats& st, int lane, const int (&tinfo)[4], const float (&v)[4][8],
+                                          int n) {
+  for (int img = st.img_lo; img <= st.img_hi; ++img) {
+    float cs[8], cq[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) cs[j] = cq[j] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const bool on = tinfo[i] >= 0 && !(tinfo[i] & 0x40000000) && st.timg[i] == img;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x = on ? v[i][j] : 0.0f;
+        cs[j] += x;
+        cq[j] = fmaf(x, x, cq[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], o);
+        cq[j] += __shfl_xor_sync(0xffffffffu, cq[j], o);
+      }
+    }
+    if (lane < 4) {
+      const int slot = st.blk - (int)(((long long)img * st.gn_rpi) >> 5);
+      float4* dst = reinterpret_cast<float4*>(
+          st.gn_part + (((long long)img * st.gn_slots + slot) * st.gn_ld + n + 8 * lane) * 2);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) dst[q] = make_float4(cs[2 * q], cq[2 * q], cs[2 * q + 1], cq[2 * q + 1]);
+    }
+  }
+}
+
 // ---- fast path ------------------------------------------------------------------------------------------
 // tinfo[i] describes tile row 8*i + lane/4 of this warp's 32 rows: -1 = skip, else out_row | border << 30.
 // Lane (r, p = lane & 3) of the transposed view owns columns [8p, 8p+8) of the 32-column chunk.
 // No residual: pack to bf16 in the row-per-thread view, transpose 32 rows x 64 B, store.
 __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t patch, int lane,
                                                  const int (&tinfo)[4], const float (&f)[32], int border,
-                                                 int n) {
+                                                 int n, const EpiStats& st) {
   {
     const uint32_t row = patch + lane * 64;
     const uint32_t sw = (lane >> 1) & 3;
@@ -196,6 +273,15 @@ __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t pat
   for (int i = 0; i < 4; ++i)
     if (tinfo[i] >= 0)
       *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u[i];
+  if (st.gn_part != nullptr) {  // statistics of the values as stored (bf16-rounded)
+    float v[4][8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[i][0] = bf16_lo(u[i].x); v[i][1] = bf16_hi(u[i].x); v[i][2] = bf16_lo(u[i].y); v[i][3] = bf16_hi(u[i].y);
+      v[i][4] = bf16_lo(u[i].z); v[i][5] = bf16_hi(u[i].z); v[i][6] = bf16_lo(u[i].w); v[i][7] = bf16_hi(u[i].w);
+    }
+    col_stats(st, lane, tinfo, v, n);
+  }
   __syncwarp();
 }
 
@@ -203,7 +289,7 @@ __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t pat
 // coalesced mapping (already in registers: issued before the TMEM load), round once, store.
 __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patch, int lane,
                                                 const int (&tinfo)[4], const float (&f)[32],
-                                                const uint4 (&res)[4], int n) {
+                                                const uint4 (&res)[4], int n, EpiStats& st) {
   {
     const uint32_t row = patch + lane * 128;
     const uint32_t sw = lane & 7;
@@ -223,23 +309,42 @@ __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patc
     lo4[i] = lds128(rowa + (((2 * p) ^ (r & 7)) << 4));
     hi4[i] = lds128(rowa + (((2 * p + 1) ^ (r & 7)) << 4));
   }
+  float v[4][8];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const uint4 lo = lo4[i], hi = hi4[i];
+    const uint4 rr = res[i];
+    v[i][0] = __uint_as_float(lo.x) + bf16_lo(rr.x); v[i][1] = __uint_as_float(lo.y) + bf16_hi(rr.x);
+    v[i][2] = __uint_as_float(lo.z) + bf16_lo(rr.y); v[i][3] = __uint_as_float(lo.w) + bf16_hi(rr.y);
+    v[i][4] = __uint_as_float(hi.x) + bf16_lo(rr.z); v[i][5] = __uint_as_float(hi.y) + bf16_hi(rr.z);
+    v[i][6] = __uint_as_float(hi.z) + bf16_lo(rr.w); v[i][7] = __uint_as_float(hi.w) + bf16_hi(rr.w);
     if (tinfo[i] >= 0) {
       uint4 u;
       if (tinfo[i] & 0x40000000) {
         u = make_uint4(0u, 0u, 0u, 0u);
       } else {
-        const uint4 rr = res[i];
-        u.x = pack_bf16x2(__uint_as_float(lo.x) + bf16_lo(rr.x), __uint_as_float(lo.y) + bf16_hi(rr.x));
-        u.y = pack_bf16x2(__uint_as_float(lo.z) + bf16_lo(rr.y), __uint_as_float(lo.w) + bf16_hi(rr.y));
-        u.z = pack_bf16x2(__uint_as_float(hi.x) + bf16_lo(rr.z), __uint_as_float(hi.y) + bf16_hi(rr.z));
-        u.w = pack_bf16x2(__uint_as_float(hi.z) + bf16_lo(rr.w), __uint_as_float(hi.w) + bf16_hi(rr.w));
+        u.x = pack_bf16x2(v[i][0], v[i][1]);
+        u.y = pack_bf16x2(v[i][2], v[i][3]);
+        u.z = pack_bf16x2(v[i][4], v[i][5]);
+        u.w = pack_bf16x2(v[i][6], v[i][7]);
       }
       *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u;
+      if (st.rows_on || st.gn_part != nullptr) {  // statistics of the values as stored (bf16-rounded)
+        v[i][0] = bf16_lo(u.x); v[i][1] = bf16_hi(u.x); v[i][2] = bf16_lo(u.y); v[i][3] = bf16_hi(u.y);
+        v[i][4] = bf16_lo(u.z); v[i][5] = bf16_hi(u.z); v[i][6] = bf16_lo(u.w); v[i][7] = bf16_hi(u.w);
+      }
     }
   }
+  if (st.rows_on) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        st.rs[i] += v[i][j];
+        st.rq[i] = fmaf(v[i][j], v[i][j], st.rq[i]);
+      }
+  }
+  if (st.gn_part != nullptr) col_stats(st, lane, tinfo, v, n);
   __syncwarp();
 }
 
@@ -307,13 +412,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     {   // all 32 lanes run the (warp-uniform) loop so that addresses stay in uniform registers;
         // one elected lane issues the TMA instructions
       uint32_t it_g = 0, s = 0, ph = 0;
-      if (kCtas == 1 && a.wstat && cluster_id < a.num_tiles) {
+      if (a.wstat && cluster_id < a.num_tiles) {
         const int pt0 = a.reverse ? a.num_tiles - 1 - cluster_id : cluster_id;
-        const int n0 = (pt0 % a.n_tiles) * a.bn;
+        const int n0 = (pt0 % a.n_tiles) * a.bn + rank * b_rows;
         if (elect_one()) {
-          mbar_expect_tx(bar_bfull, wstat_bytes);
-          for (int kc = 0; kc < a.kchunks; ++kc)
-            tma_load_2d(tiles_base + kc * b_bytes, &tmB, bar_bfull, kc * BK, n0);
+          if (kCtas == 2) {   // each CTA keeps its half of the weight rows; all bytes are counted on the leader's barrier
+            const uint32_t fb = mapa_cluster(bar_bfull, 0);
+            if (rank == 0) mbar_expect_tx(bar_bfull, wstat_bytes * 2);
+            for (int kc = 0; kc < a.kchunks; ++kc)
+              tma_load_2d_pair(tiles_base + kc * b_bytes, &tmB, fb, kc * BK, n0);
+          } else {
+            mbar_expect_tx(bar_bfull, wstat_bytes);
+            for (int kc = 0; kc < a.kchunks; ++kc)
+              tma_load_2d(tiles_base + kc * b_bytes, &tmB, bar_bfull, kc * BK, n0);
+          }
         }
         __syncwarp();
       }
@@ -333,6 +445,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               } else if (kCtas == 1 && a.wstat) {
                 mbar_expect_tx(bar_full + 8 * s, a_bytes);
                 tma_load_2d(sa, &tmA, bar_full + 8 * s, kc * BK, m0 + off);
+              } else if (kCtas == 2 && a.wstat) {
+                const uint32_t fb = mapa_cluster(bar_full + 8 * s, 0);
+                if (rank == 0) mbar_expect_tx(bar_full + 8 * s, a_bytes * 2);
+                tma_load_2d_pair(sa, &tmA, fb, kc * BK, m0 + off);
               } else if (kCtas == 2) {
                 // both CTAs' bytes are counted on the leader's barrier (the MMA issuer waits there)
                 const uint32_t fb = mapa_cluster(bar_full + 8 * s, 0);
@@ -363,7 +479,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (rank == 0) {   // whole warp loops (uniform); one elected lane issues
       const uint32_t idesc = make_idesc_bf16(BM * kCtas, a.bn, 0, 0);
       uint32_t tl = 0, s = 0, ph = 0;
-      if (kCtas == 1 && a.wstat && cluster_id < a.num_tiles) mbar_wait(bar_bfull, 0);
+      if (a.wstat && cluster_id < a.num_tiles) mbar_wait(bar_bfull, 0);
       for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
         const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
         mbar_wait(bar_tempty + 8 * as, aph ^ 1);
@@ -374,7 +490,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tc_fence_after();
           const uint32_t sa = ring_base + s * stage_bytes;
           const uint64_t adesc = make_sdesc_sw128(sa, 16, 1024);
-          const uint64_t bdesc = make_sdesc_sw128((kCtas == 1 && a.wstat) ? tiles_base + it * b_bytes : sa + a_bytes, 16, 1024);
+          const uint64_t bdesc = make_sdesc_sw128(a.wstat ? tiles_base + it * b_bytes : sa + a_bytes, 16, 1024);
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
@@ -435,19 +551,69 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       return r;
     };
-    // (reading these ahead of the TMEM-load wait was measured slower: 182 vs 179 us at 217728x960x320)
-    auto add_slot32 = [&](uint32_t saddr, float (&f)[32]) {
+    const bool ln_fold = a.fast && a.ln_in != nullptr;
+    auto fetch_cs = [&](int tile_) -> float4 {  // LayerNorm column sums, same lane -> column map as fetch_cb
+      float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!ln_fold || tile_ >= a.num_tiles) return r;
+      if (a.reverse) tile_ = a.num_tiles - 1 - tile_;
+      int o = 4 * lane, twin = 0;
+      if (a.geglu && o >= 64) { o -= 64; twin = a.bn / 2; }
+      if (o >= seg_len || (a.geglu && 4 * lane >= 128)) return r;
+      const int n = (tile_ % a.n_tiles) * a.bn + seg_lo + o + twin;
+      if (n >= a.N) return r;
+      return __ldg(reinterpret_cast<const float4*>(a.ln_colsum + n));
+    };
+    // val = rstd * acc + (nmr * colsum[n] + bias'[n]),  nmr = -mean * rstd  (LayerNorm folded into the epilogue)
+    auto ln_slot32 = [&](uint32_t saddr, float (&f)[32], float rstd, float nmr) {
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         const uint4 b = lds128(saddr + 16 * q);
-        f[4 * q + 0] += __uint_as_float(b.x);
-        f[4 * q + 1] += __uint_as_float(b.y);
-        f[4 * q + 2] += __uint_as_float(b.z);
-        f[4 * q + 3] += __uint_as_float(b.w);
+        const uint4 cs = lds128(saddr + 512 + 16 * q);
+        f[4 * q + 0] = fmaf(f[4 * q + 0], rstd, fmaf(nmr, __uint_as_float(cs.x), __uint_as_float(b.x)));
+        f[4 * q + 1] = fmaf(f[4 * q + 1], rstd, fmaf(nmr, __uint_as_float(cs.y), __uint_as_float(b.y)));
+        f[4 * q + 2] = fmaf(f[4 * q + 2], rstd, fmaf(nmr, __uint_as_float(cs.z), __uint_as_float(b.z)));
+        f[4 * q + 3] = fmaf(f[4 * q + 3], rstd, fmaf(nmr, __uint_as_float(cs.w), __uint_as_float(b.w)));
+      }
+    };
+    // row partials (sum, sum of squares) of tile `tile_`'s row of this thread, one tile ahead
+    float2 ln_st[kMaxLnSlots];
+    auto fetch_ln = [&](int tile_) {
+      if (!ln_fold) return;
+      long long mrow = -1;
+      if (tile_ < a.num_tiles) {
+        const int pt_ = a.reverse ? a.num_tiles - 1 - tile_ : tile_;
+        mrow = (long long)(pt_ / a.n_tiles) * (BM * kCtas) + rank * BM + row_in_tile;
+        if (mrow >= a.M) mrow = -1;
+      }
+#pragma unroll
+      for (int sidx = 0; sidx < kMaxLnSlots; ++sidx) {
+        ln_st[sidx] = make_float2(0.f, 0.f);
+        if (sidx < a.ln_slots && mrow >= 0) ln_st[sidx] = __ldg(a.ln_in + (long long)sidx * a.M + mrow);
+      }
+    };
+    // (reading these ahead of the TMEM-load wait was measured slower: 182 vs 179 us at 217728x960x320)
+    auto add_slot32 = [&](uint32_t saddr, float (&f)[32]) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {  // packed adds: half the fma-pipe issue slots of 32 scalar FADDs
+        const uint4 b = lds128(saddr + 16 * q);
+        const unsigned long long s0 = add2(pk2(f[4 * q + 0], f[4 * q + 1]), pk2(__uint_as_float(b.x), __uint_as_float(b.y)));
+        const unsigned long long s1 = add2(pk2(f[4 * q + 2], f[4 * q + 3]), pk2(__uint_as_float(b.z), __uint_as_float(b.w)));
+        f[4 * q + 0] = lo2(s0);
+        f[4 * q + 1] = hi2(s0);
+        f[4 * q + 2] = lo2(s1);
+        f[4 * q + 3] = hi2(s1);
       }
     };
 
     float4 cb_next = fetch_cb(cluster_id);
+    float4 cs_next = fetch_cs(cluster_id);
+    fetch_ln(cluster_id);
+    EpiStats st;
+    st.gn_part = a.fast ? a.gn_part : nullptr;
+    st.gn_ld = a.Nout;
+    st.gn_slots = a.gn_slots;
+    st.gn_rpi = a.gn_rpi;
+    st.rows_on = a.fast && a.ln_rows != nullptr && a.residual != nullptr;
     uint32_t tl = 0;
     for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
       const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
@@ -459,9 +625,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (has_cb) {
         sts128(bslot + 16 * lane, __float_as_uint(cb_next.x), __float_as_uint(cb_next.y),
                __float_as_uint(cb_next.z), __float_as_uint(cb_next.w));
+        if (ln_fold)
+          sts128(bslot + 512 + 16 * lane, __float_as_uint(cs_next.x), __float_as_uint(cs_next.y),
+                 __float_as_uint(cs_next.z), __float_as_uint(cs_next.w));
         __syncwarp();
         cb_next = fetch_cb(tile + n_clusters);
+        cs_next = fetch_cs(tile + n_clusters);
       }
+      float ln_rstd = 0.0f, ln_nmr = 0.0f;
+      if (ln_fold) {
+        float ssum = 0.0f, qsum = 0.0f;
+#pragma unroll
+        for (int sidx = 0; sidx < kMaxLnSlots; ++sidx) {
+          ssum += ln_st[sidx].x;
+          qsum += ln_st[sidx].y;
+        }
+        const float mean = ssum * a.ln_inv_c;
+        const float var = fmaxf(fmaf(qsum, a.ln_inv_c, -mean * mean), 0.0f);
+        ln_rstd = rsqrtf(var + a.ln_eps);
+        ln_nmr = -mean * ln_rstd;
+        fetch_ln(tile + n_clusters);
+      }
+      float row_s = 0.0f, row_q = 0.0f;  // LayerNorm row partial of this thread's row (plain path)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) st.rs[i] = st.rq[i] = 0.0f;
       RowInfo ri;
       ri.valid = m < a.M;
       ri.border = 0;
@@ -496,6 +683,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
         for (int i = 0; i < 4; ++i) tinfo[i] = __shfl_sync(0xffffffffu, info, 8 * i + (lane >> 2));
       }
+      if (st.gn_part != nullptr) {
+        const int img = ri.valid ? m / a.gn_rpi : -1;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) st.timg[i] = __shfl_sync(0xffffffffu, img, 8 * i + (lane >> 2));
+        const int mfirst = m0 + quarter * 32;  // warp-uniform
+        const int mlast = min(mfirst + 31, a.M - 1);
+        st.blk = mfirst >> 5;
+        st.img_lo = mfirst < a.M ? mfirst / a.gn_rpi : 0;
+        st.img_hi = mfirst < a.M ? mlast / a.gn_rpi : -1;
+      }
 
       const uint32_t taddr = tmem_base + as * 256 + (uint32_t(quarter * 32) << 16);
       // release of this accumulator stage: after this warp's last TMEM load of the tile
@@ -511,6 +708,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (u_begin >= u_end) {
         mbar_wait(bar_tfull + 8 * as, aph);
         release_tmem();
+        if (a.fast && a.ln_rows != nullptr && ri.valid)  // a part without columns still owns its slot
+          a.ln_rows[(long long)(tile_n * kParts + part) * a.M + m] = make_float2(0.f, 0.f);
       } else if (!a.geglu) {
         for (int c = u_begin; c < u_end; ++c) {
           const int n = n0 + c * 32;
@@ -538,7 +737,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
           if (a.fast) {
-            if (has_cb) add_slot32(bslot + (c - u_begin) * 128, f);
+            if (ln_fold) ln_slot32(bslot + (c - u_begin) * 128, f, ln_rstd, ln_nmr);
+            else if (has_cb) add_slot32(bslot + (c - u_begin) * 128, f);
             if (rb_fix) {  // rare: rows of two row groups in one warp tile
               const float* r1 = a.rowbias + (long long)ri.rb_group * a.Nout + n;
               int mf = m0 + quarter * 32;
@@ -547,8 +747,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
               for (int j = 0; j < 32; ++j) f[j] += __ldg(r1 + j) - __ldg(r0 + j);
             }
-            if (a.residual != nullptr) store_chunk_res(a, patch, lane, tinfo, f, res, n);
-            else store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n);
+            if (a.residual != nullptr) {
+              store_chunk_res(a, patch, lane, tinfo, f, res, n, st);
+            } else {
+              if (a.ln_rows != nullptr) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  const float r = __bfloat162float(__float2bfloat16(f[j]));  // the value as stored
+                  row_s += r;
+                  row_q = fmaf(r, r, row_q);
+                }
+              }
+              store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n, st);
+            }
           } else {
             if (a.bias != nullptr) {
 #pragma unroll
@@ -556,6 +767,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 if (n + j < a.N) f[j] += __ldg(a.bias + n + j);
             }
             finish_store32(a, ri, f, n);
+          }
+        }
+        if (a.fast && a.ln_rows != nullptr) {
+          float2* dst = a.ln_rows + (long long)(tile_n * kParts + part) * a.M;
+          if (a.residual != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              float s1 = st.rs[i], q1 = st.rq[i];
+              s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
+              q1 += __shfl_xor_sync(0xffffffffu, q1, 1);
+              s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+              q1 += __shfl_xor_sync(0xffffffffu, q1, 2);
+              const int mr = m0 + quarter * 32 + 8 * i + (lane >> 2);
+              if ((lane & 3) == 0 && mr < a.M) dst[mr] = make_float2(s1, q1);
+            }
+          } else if (ri.valid) {
+            dst[m] = make_float2(row_s, row_q);
           }
         }
       } else {
@@ -575,7 +803,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             g[j] = __uint_as_float(vg[j]);
           }
           if (a.fast) {
-            if (has_cb) {
+            if (ln_fold) {
+              ln_slot32(bslot + (p - u_begin) * 128, f, ln_rstd, ln_nmr);
+              ln_slot32(bslot + 256 + (p - u_begin) * 128, g, ln_rstd, ln_nmr);
+            } else if (has_cb) {
               add_slot32(bslot + (p - u_begin) * 128, f);
               add_slot32(bslot + 256 + (p - u_begin) * 128, g);
             }
@@ -591,7 +822,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
           for (int j = 0; j < 32; j += 2) geglu2(f[j], f[j + 1], g[j], g[j + 1]);
           const int n_out = tile_n * (a.bn / 2) + p * 32;
-          if (a.fast) store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n_out);
+          if (a.fast) store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n_out, st);
           else finish_store32(a, ri, f, n_out);
         }
       }
@@ -627,6 +858,14 @@ static int pick_bn(int N, int geglu) {
 }  // namespace seva
 
 extern "C" int seva_gemm_pick_bn(int32_t N, int32_t geglu) { return seva::pick_bn(N, geglu); }
+
+// Row-statistic slots a GEMM with N output columns (N tile bn, 0 = the default choice) writes per row when
+// SevaGemm.ln_rowstats is set: one per (N tile, epilogue column share).
+extern "C" int seva_gemm_ln_slots(int32_t N, int32_t bn) {
+  if (N <= 0) return -1;
+  if (bn <= 0) bn = seva::pick_bn(N, 0);
+  return ((N + bn - 1) / bn) * (seva::kEpiWarps / 4);
+}
 
 extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   using namespace seva;
@@ -679,6 +918,15 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   a.Hp = g->Hp;
   a.Wp = g->Wp;
   a.reverse = g->reverse != 0;
+  a.gn_part = g->gn_partial;
+  a.gn_rpi = g->gn_rpi;
+  a.gn_slots = g->gn_slots;
+  a.ln_rows = reinterpret_cast<float2*>(g->ln_rowstats);
+  a.ln_in = reinterpret_cast<const float2*>(g->ln_in_stats);
+  a.ln_slots = g->ln_in_slots;
+  a.ln_eps = g->ln_eps;
+  a.ln_inv_c = 1.0f / (float)g->Kc;
+  a.ln_colsum = g->ln_colsum;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
 #ifdef SEVA_DEBUG
   {
@@ -692,17 +940,49 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
            (g->bias == nullptr || al16(g->bias)) && (g->rowbias == nullptr || al16(g->rowbias)) &&
            (g->residual == nullptr || ((g->ldr % 8) == 0 && al16(g->residual)));
 
+  if (g->gn_partial != nullptr || g->ln_rowstats != nullptr || g->ln_in_stats != nullptr)
+    SEVA_CHECK(a.fast, "seva_gemm_bf16: output statistics / LayerNorm folding need the coalesced bf16 epilogue "
+                       "(bf16 output, N %% 32 == 0, 16-byte aligned pointers and strides)");
+  if (g->gn_partial != nullptr) {
+    SEVA_CHECK(!g->geglu && g->gn_rpi > 0 && g->gn_slots == (g->gn_rpi + 31) / 32 + 1 && al16(g->gn_partial),
+               "seva_gemm_bf16: gn_partial needs gn_rpi > 0, gn_slots = ceil(gn_rpi / 32) + 1, 16-byte alignment, no GEGLU");
+  }
+  if (g->ln_rowstats != nullptr)
+    SEVA_CHECK(!g->geglu && g->out_map == 0 && !g->mask_border && (reinterpret_cast<uintptr_t>(g->ln_rowstats) & 7) == 0,
+               "seva_gemm_bf16: ln_rowstats is for plain row-mapped outputs");
+  if (g->ln_in_stats != nullptr) {
+    SEVA_CHECK(g->ntaps == 1 && g->bias != nullptr && g->ln_colsum != nullptr && g->rowbias == nullptr && al16(g->ln_colsum) &&
+                   g->ln_in_slots > 0 && g->ln_in_slots <= kMaxLnSlots && (reinterpret_cast<uintptr_t>(g->ln_in_stats) & 7) == 0,
+               "seva_gemm_bf16: LayerNorm folding needs bias (beta.W + b), ln_colsum, 1..%d row-statistic slots and no rowbias",
+               kMaxLnSlots);
+  }
+
   // CTA pair (256-row tiles, half the weight rows per CTA) once the main loop is long enough for the operand
   // traffic to matter (measured cross-over: K*taps around 1024); short-K problems are epilogue/HBM-bound and
   // keep the finer 128-row granularity.
   const int sms = sm_count();
+  const int sms_of = sms;
+  const int fixed = kCtrlBytes + 1024 + kEpiWarps * (kPatchBytes + kBiasSlotBytes);
+  // weight-stationary walk feasible with `c` CTAs per tile?  single tap, K a multiple of 64, the per-CTA share of the
+  // [bn, K] weight tile plus at least 3 A stages fit, and there are enough M tiles to give every N tile its own CTAs
+  auto wstat_ok = [&](int c) {
+    const int units = sms_of / c, mt = (g->M + BM * c - 1) / (BM * c);
+    const int wb = a.kchunks * (bn / c) * BK * 2;
+    return g->ntaps == 1 && (g->Kc % BK) == 0 && a.n_tiles <= units && mt >= 2 * (units / a.n_tiles) &&
+           fixed + wb + 3 * (BM * BK * 2) <= kSmemMax;
+  };
   int ctas = g->cluster;
-  if (ctas == 0) ctas = ((long long)g->ntaps * g->Kc >= 1024 && g->M > BM) ? 2 : 1;
+  if (ctas == 0) {
+    ctas = ((long long)g->ntaps * g->Kc >= 1024 && g->M > BM) ? 2 : 1;
+    // short K, wide N (the GEGLU projection at K = 320): a single CTA cannot keep the 160 KB weight tile resident and
+    // re-reads A + W (240 KB) from L2 for every 128 x 256 tile -- 41 B/clk/SM measured, the L2 limit.  A CTA pair
+    // holds half the weight rows each (80 KB) and streams only its own A rows: 80 KB per tile.
+    if (ctas == 1 && g->M > 2 * BM && !wstat_ok(1) && wstat_ok(2)) ctas = 2;
+  }
   const int m_tiles = (g->M + BM * ctas - 1) / (BM * ctas);
   a.num_tiles = m_tiles * a.n_tiles;
   const int b_rows = bn / ctas;
   const int stage_bytes = BM * BK * 2 + b_rows * BK * 2;
-  const int fixed = kCtrlBytes + 1024 + kEpiWarps * (kPatchBytes + kBiasSlotBytes);
   int stages = (kSmemMax - fixed) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   // Weight-stationary walk (SEVA_WSTAT=0 turns it off): short-K single-tap problems whose [bn, K] weight tile and
@@ -716,12 +996,12 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
 #else
     constexpr int want = 1;
 #endif
-    const int a_bytes = BM * BK * 2, wb = a.kchunks * bn * BK * 2;
-    if (want && ctas == 1 && g->ntaps == 1 && (g->Kc % BK) == 0 && a.n_tiles <= sms && m_tiles >= 2 * (sms / a.n_tiles) &&
-        fixed + wb + 3 * a_bytes <= kSmemMax) {
+    const int a_bytes = BM * BK * 2, wb = a.kchunks * b_rows * BK * 2;
+    if (want && wstat_ok(ctas)) {
+      const int units = sms / ctas;
       a.wstat = 1;
       wstat_bytes = wb;
-      wstat_grid = (sms / a.n_tiles) * a.n_tiles;
+      wstat_grid = (units / a.n_tiles) * a.n_tiles;   // clusters
       stages = (kSmemMax - fixed - wb) / a_bytes;
       if (stages > kMaxStages) stages = kMaxStages;
     }
@@ -754,6 +1034,7 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   } else {
     int pairs = sms / 2;
     if (pairs > a.num_tiles) pairs = a.num_tiles;
+    if (a.wstat) pairs = wstat_grid;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * pairs);
     cfg.blockDim = dim3(kGemmThreads);

@@ -127,6 +127,7 @@ struct GNApplyArgs {
   const float* dense;
   const float* dense_w;
   const float* dense_b;
+  const float* gstats;  // [Nimg][groups][2] (mean, rstd) from seva_groupnorm_finalize; when set, `sums` is not read
 };
 
 typedef unsigned long long f2_t;  // two packed fp32
@@ -157,6 +158,12 @@ gn_apply_kernel(const GNApplyArgs a) {
   const int Wp = a.W + 2;
   const long long rpi_pad = (long long)(a.H + 2) * Wp;
   for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
+    if (a.gstats != nullptr) {
+      const float2 v = __ldcg(reinterpret_cast<const float2*>(a.gstats) + (long long)n * a.groups + g);
+      gstat[2 * g] = v.x;
+      gstat[2 * g + 1] = v.y;
+      continue;
+    }
     const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
     float s = 0.f, q = 0.f;
 #pragma unroll 8
@@ -165,11 +172,12 @@ gn_apply_kernel(const GNApplyArgs a) {
       s += v.x;
       q += v.y;
     }
-    const float cnt = (float)cpg * (float)HW;
-    const float mean = s / cnt;
-    const float var = fmaxf(q / cnt - mean * mean, 0.0f);
-    gstat[2 * g] = mean;
-    gstat[2 * g + 1] = rsqrtf(var + a.eps);
+    // fp64 for the final E[x^2] - mean^2: the fp32 sums are each good to ~1e-7 relative, the subtraction is not
+    const double cnt = (double)cpg * (double)HW;
+    const double mean = (double)s / cnt;
+    const double var = fmax((double)q / cnt - mean * mean, 0.0);
+    gstat[2 * g] = (float)mean;
+    gstat[2 * g + 1] = (float)(1.0 / sqrt(var + (double)a.eps));
   }
   __syncthreads();
 
@@ -326,6 +334,12 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
   for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
+    if (a.gstats != nullptr) {
+      const float2 v = __ldcg(reinterpret_cast<const float2*>(a.gstats) + (long long)n * a.groups + g);
+      gstat[2 * g] = v.x;
+      gstat[2 * g + 1] = v.y;
+      continue;
+    }
     const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
     float s = 0.f, q = 0.f;
 #pragma unroll 8
@@ -334,11 +348,12 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
       s += v.x;
       q += v.y;
     }
-    const float cnt = (float)cpg * (float)HW;
-    const float mean = s / cnt;
-    const float var = fmaxf(q / cnt - mean * mean, 0.0f);
-    gstat[2 * g] = mean;
-    gstat[2 * g + 1] = rsqrtf(var + a.eps);
+    // fp64 for the final E[x^2] - mean^2: the fp32 sums are each good to ~1e-7 relative, the subtraction is not
+    const double cnt = (double)cpg * (double)HW;
+    const double mean = (double)s / cnt;
+    const double var = fmax((double)q / cnt - mean * mean, 0.0);
+    gstat[2 * g] = (float)mean;
+    gstat[2 * g + 1] = (float)(1.0 / sqrt(var + (double)a.eps));
   }
   const uint32_t ring = ring_base + threadIdx.x * 8;
   const uint32_t ring_pitch = blockDim.x * 8;
@@ -495,6 +510,75 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
       const long long row = out_img + (long long)yy * Wp + xx;
       *reinterpret_cast<uint2*>(a.y + row * a.ldy + c0) = make_uint2(0u, 0u);
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// GroupNorm finalize: folds the per-32-row-block partial statistics that the PRODUCING GEMM's epilogue wrote
+// (SevaGemm.gn_partial) into per-(image, group) mean / rstd.  Up to two sources side by side along the channel axis
+// (the virtual skip concat of the decoder: each producer has its own row space and slot count; groups may straddle
+// the seam).  One block per (image, group range); partials are summed in slot order in fp64, so the result
+// is deterministic and the E[x^2] - mean^2 cancellation happens in double precision.
+// ------------------------------------------------------------------------------------------------
+struct GNFinalizeArgs {
+  const float* part[2];
+  int C[2], rpi[2], slots[2];
+  int groups, cpg, gpb;   // groups per block
+  double inv_cnt;
+  float eps;
+  float* gstats;          // [Nimg][groups][2]
+};
+
+constexpr int kFinLanes = 8;  // slot lanes per channel: lane j sums slots j, j + 8, ... in order; lanes are then added in order
+
+__global__ void __launch_bounds__(256)
+gn_finalize_kernel(const GNFinalizeArgs a) {
+  extern __shared__ double ch[];  // [kFinLanes][channels of this block][2]
+  const int n = blockIdx.y;
+  const int g0 = blockIdx.x * a.gpb;
+  const int ng = min(a.gpb, a.groups - g0);
+  const int c_begin = g0 * a.cpg, nch = ng * a.cpg;
+  const int lane_s = threadIdx.x / 32;       // slot lane (8 warps)
+  const int lane_c = threadIdx.x & 31;       // channel lane
+  for (int cc = lane_c; cc < nch; cc += 32) {
+    const int c = c_begin + cc;
+    const int src = c < a.C[0] ? 0 : 1;
+    const int cl = c - (src ? a.C[0] : 0);
+    const int Cs = a.C[src];
+    const long long first = ((long long)n * a.rpi[src]) >> 5;
+    const long long last = ((long long)(n + 1) * a.rpi[src] - 1) >> 5;
+    const int cnt = (int)(last - first) + 1;
+    const float2* p = reinterpret_cast<const float2*>(a.part[src]) + ((long long)n * a.slots[src]) * Cs + cl;
+    double s = 0.0, q = 0.0;
+    int k = lane_s;
+    for (; k + 3 * kFinLanes < cnt; k += 4 * kFinLanes) {  // 4 independent loads in flight, added in slot order
+      const float2 v0 = __ldcg(p + (long long)k * Cs), v1 = __ldcg(p + (long long)(k + kFinLanes) * Cs);
+      const float2 v2 = __ldcg(p + (long long)(k + 2 * kFinLanes) * Cs), v3 = __ldcg(p + (long long)(k + 3 * kFinLanes) * Cs);
+      s += (double)v0.x; q += (double)v0.y;
+      s += (double)v1.x; q += (double)v1.y;
+      s += (double)v2.x; q += (double)v2.y;
+      s += (double)v3.x; q += (double)v3.y;
+    }
+    for (; k < cnt; k += kFinLanes) {
+      const float2 v = __ldcg(p + (long long)k * Cs);
+      s += (double)v.x;
+      q += (double)v.y;
+    }
+    ch[2 * (lane_s * nch + cc)] = s;
+    ch[2 * (lane_s * nch + cc) + 1] = q;
+  }
+  __syncthreads();
+  for (int g = threadIdx.x; g < ng; g += blockDim.x) {
+    double s = 0.0, q = 0.0;
+    for (int c = 0; c < a.cpg; ++c)
+      for (int j = 0; j < kFinLanes; ++j) {
+        s += ch[2 * (j * nch + g * a.cpg + c)];
+        q += ch[2 * (j * nch + g * a.cpg + c) + 1];
+      }
+    const double mean = s * a.inv_cnt;
+    const double var = fmax(q * a.inv_cnt - mean * mean, 0.0);
+    float2* dst = reinterpret_cast<float2*>(a.gstats) + (long long)n * a.groups + g0 + g;
+    *dst = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)a.eps)));
   }
 }
 
@@ -669,11 +753,53 @@ extern "C" int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, in
   return 0;
 }
 
+extern "C" int seva_groupnorm_partial_floats(int32_t Nimg, int32_t rpi, int32_t C) {
+  if (Nimg <= 0 || rpi <= 0 || C <= 0) return -1;
+  const long long n = (long long)Nimg * ((rpi + 31) / 32 + 1) * C * 2;
+  return n > 0x7fffffffll ? -1 : (int)n;
+}
+
+extern "C" int seva_groupnorm_finalize(const float* part0, int32_t C0, int32_t rpi0, const float* part1, int32_t C1,
+                                       int32_t rpi1, int32_t Nimg, int32_t groups, int32_t pixels, float eps,
+                                       float* gstats, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(part0 && gstats && C0 > 0 && rpi0 > 0 && Nimg > 0 && groups > 0 && pixels > 0,
+             "seva_groupnorm_finalize: bad arguments");
+  SEVA_CHECK((part1 == nullptr) == (C1 == 0) && (part1 == nullptr || rpi1 > 0), "seva_groupnorm_finalize: bad second source");
+  const int C = C0 + C1;
+  SEVA_CHECK((C % groups) == 0, "seva_groupnorm_finalize: %d channels do not split into %d groups", C, groups);
+  GNFinalizeArgs a;
+  a.part[0] = part0; a.part[1] = part1;
+  a.C[0] = C0; a.C[1] = C1;
+  a.rpi[0] = rpi0; a.rpi[1] = rpi1 > 0 ? rpi1 : 1;
+  a.slots[0] = (rpi0 + 31) / 32 + 1;
+  a.slots[1] = (a.rpi[1] + 31) / 32 + 1;
+  a.groups = groups;
+  a.cpg = C / groups;
+  // ~32 channels per block (whole groups only): 8 warps split the slots of a channel, so even the 172 slots of a
+  // 72 x 72 image are 6 rounds of loads; Nimg x (C / 32) blocks
+  int gpb = 32 / a.cpg;
+  if (gpb < 1) gpb = 1;
+  if (gpb > groups) gpb = groups;
+  a.gpb = gpb;
+  a.inv_cnt = 1.0 / ((double)a.cpg * (double)pixels);
+  a.eps = eps;
+  a.gstats = gstats;
+  const size_t smem = sizeof(double) * 2 * kFinLanes * (size_t)gpb * a.cpg;
+  SEVA_CHECK(smem <= 40 * 1024, "seva_groupnorm_finalize: group of %d channels too wide", a.cpg);
+  dim3 grid((groups + gpb - 1) / gpb, Nimg);
+  gn_finalize_kernel<<<grid, 256, smem, stream>>>(a);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   using namespace seva;
   if (check_device()) return 3;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
-  SEVA_CHECK(p && p->x && p->y && p->sums && p->gamma && p->beta, "seva_groupnorm_apply: null pointer");
+  SEVA_CHECK(p && p->x && p->y && (p->sums || p->gstats) && p->gamma && p->beta, "seva_groupnorm_apply: null pointer");
   SEVA_CHECK(p->C > 0 && p->groups > 0 && (p->C % p->groups) == 0 && (p->C % 4) == 0,
              "seva_groupnorm_apply: bad C=%d groups=%d", p->C, p->groups);
   SEVA_CHECK((p->ldx % 4) == 0 && (p->ldy % 4) == 0, "seva_groupnorm_apply: ldx/ldy must be multiples of 4");
@@ -699,6 +825,7 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   a.dense = p->dense;
   a.dense_w = p->dense_w;
   a.dense_b = p->dense_b;
+  a.gstats = p->gstats;
   a.reverse = p->reverse != 0;
   // dense modulation keeps 4x2x6 weights per thread in registers -> 4-channel vectors (8-byte accesses);
   // the plain path uses 8-channel vectors (16-byte accesses) when the strides allow it

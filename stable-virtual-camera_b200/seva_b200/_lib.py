@@ -26,6 +26,8 @@ class SevaGemm(C.Structure):
         ("out_fp32", c_int), ("geglu", c_int), ("out_map", c_int), ("H", c_int), ("Wd", c_int),
         ("mask_border", c_int), ("Hp", c_int), ("Wp", c_int), ("bn", c_int), ("cluster", c_int),
         ("reverse", c_int),
+        ("gn_partial", c_void_p), ("gn_rpi", c_int), ("gn_slots", c_int), ("ln_rowstats", c_void_p),
+        ("ln_in_stats", c_void_p), ("ln_in_slots", c_int), ("ln_eps", c_float), ("ln_colsum", c_void_p),
     ]
 
 
@@ -36,6 +38,7 @@ class SevaGNApply(C.Structure):
         ("Nimg", c_int), ("H", c_int), ("Wd", c_int), ("C", c_int), ("groups", c_int),
         ("eps", c_float), ("in_padded", c_int), ("out_padded", c_int), ("silu", c_int),
         ("dense", c_void_p), ("dense_w", c_void_p), ("dense_b", c_void_p), ("reverse", c_int),
+        ("gstats", c_void_p),
     ]
 
 
@@ -50,12 +53,18 @@ _PROTOS = {
     "seva_version": [],
     "seva_gemm_bf16": [C.POINTER(SevaGemm), c_void_p],
     "seva_gemm_pick_bn": [c_int, c_int],
+    "seva_gemm_ln_slots": [c_int, c_int],
     "seva_attn_fwd": [c_void_p] * 4 + [c_int] * 4 + [c_i64] * 8 + [c_float, c_void_p],
+    "seva_attn_partial": [c_void_p] * 5 + [c_int] * 4 + [c_i64] * 6 + [c_float, c_void_p],
+    "seva_attn_merge": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_i64, c_i64, c_void_p],
     "seva_timemix_attn": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_i64, c_i64, c_float, c_void_p],
     "seva_timemix_attn_kv": [c_void_p] * 4 + [c_int] * 5 + [c_i64] * 3 + [c_float, c_void_p],
     "seva_groupnorm_stats_floats": [c_int, c_int, c_int],
     "seva_groupnorm_stats": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_int, c_void_p],
     "seva_groupnorm_apply": [C.POINTER(SevaGNApply), c_void_p],
+    "seva_groupnorm_partial_floats": [c_int, c_int, c_int],
+    "seva_groupnorm_finalize": [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p,
+                                c_void_p],
     "seva_layernorm": [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p],
     "seva_plucker": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     "seva_resize_bilinear_ac": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],

@@ -53,6 +53,45 @@ def _pack_ln(ln):
     return dict(g=_f32(ln.weight), b=_f32(ln.bias), eps=float(ln.eps))
 
 
+# LayerNorm folded into the consuming GEMM's epilogue.  Opt-in: measured SLOWER in the step (r2b/r2c: the K = 320 GEGLU goes
+# 468 -> 683 us, qkv 185 -> 283 us -- these GEMMs are epilogue-bound and the fold adds 2 FFMA + 1 LDS.128 per 4 values
+# there, which costs more than the 24 us LayerNorm launch it removes).
+LN_FOLD = os.environ.get("SEVA_LN_FOLD", "0") != "0"
+FUSED_GN_STATS = os.environ.get("SEVA_GN_FUSED_STATS", "1") != "0"  # GroupNorm statistics from the producing GEMM
+
+
+def _can_fold(C_: int) -> bool:
+    return LN_FOLD and C_ % 32 == 0 and 0 < ops.ln_slots(C_) <= 10
+
+
+def _fold_ln_linear(ln, w, b):
+    """Linear(LayerNorm(x)) = rstd * (x . (W gamma)^T - mean * colsum) + (W beta + b):
+    returns (W * gamma in bf16, colsum of the ROUNDED folded weight (what the tensor cores multiply), W beta + b)."""
+    wf = w.detach().float()
+    wg = (wf * ln.weight.detach().float()[None]).to(torch.bfloat16)
+    bias2 = wf @ ln.bias.detach().float()
+    if b is not None:
+        bias2 = bias2 + b.detach().float()
+    return wg.contiguous(), wg.float().sum(1).contiguous(), bias2.contiguous()
+
+
+def _pack_ff_ln(ff, ln):
+    """FeedForward whose input LayerNorm is folded into the GEGLU projection."""
+    w, b = ff.net[0].proj.weight, ff.net[0].proj.bias
+    bn = ops.pick_bn(w.shape[0], True)
+    wg, colsum, bias2 = _fold_ln_linear(ln, w, b)
+    wp, bp = pack.pack_geglu(wg, bias2, bn)
+    _, cp = pack.pack_geglu(wg, colsum, bn)
+    return dict(w1=wp, b1=bp, cs1=cp, bn1=bn, eps=float(ln.eps), w2=pack.pack_linear(ff.net[2].weight),
+                b2=_f32(ff.net[2].bias))
+
+
+def _pack_attn_self_ln(at, ln):
+    wg, colsum, bias2 = _fold_ln_linear(ln, torch.cat([at.to_q.weight, at.to_k.weight, at.to_v.weight], 0), None)
+    return dict(wqkv=wg, csqkv=colsum, bqkv=bias2, eps=float(ln.eps), wo=pack.pack_linear(at.to_out[0].weight),
+                bo=_f32(at.to_out[0].bias))
+
+
 def pack_weights(model: Seva) -> dict:
     """id(module) -> dict of kernel-layout tensors (bf16 K-major matrices, fp32 vectors)."""
     dev = next(model.parameters()).device
@@ -82,15 +121,21 @@ def pack_weights(model: Seva) -> dict:
             elif isinstance(m, MultiviewTransformer):
                 assert len(m.transformer_blocks) == 1, "transformer depth > 1 is not wired into the plan yet"
                 tb, tm = m.transformer_blocks[0], m.time_mix_blocks[0]
+                fold = _can_fold(m.in_channels)
                 P[id(m)] = dict(
                     gn=dict(g=_f32(m.norm.weight), b=_f32(m.norm.bias), eps=float(m.norm.eps)),
                     win=pack.pack_linear(m.proj_in.weight), bin=_f32(m.proj_in.bias),
                     wout=pack.pack_linear(m.proj_out.weight), bout=_f32(m.proj_out.bias),
-                    s_attn1=_pack_attn_self(tb.attn1), s_attn2=_pack_attn_cross(tb.attn2), s_ff=_pack_ff(tb.ff, dev),
+                    s_attn1=_pack_attn_self_ln(tb.attn1, tb.norm1) if fold else _pack_attn_self(tb.attn1),
+                    s_attn2=_pack_attn_cross(tb.attn2),
+                    s_ff=_pack_ff_ln(tb.ff, tb.norm3) if fold else _pack_ff(tb.ff, dev),
                     s_n1=_pack_ln(tb.norm1), s_n2=_pack_ln(tb.norm2), s_n3=_pack_ln(tb.norm3),
-                    t_nin=_pack_ln(tm.norm_in), t_ffin=_pack_ff(tm.ff_in, dev), t_attn1=_pack_attn_self(tm.attn1),
-                    t_attn2=_pack_attn_cross(tm.attn2), t_ff=_pack_ff(tm.ff, dev),
-                    t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3))
+                    t_nin=_pack_ln(tm.norm_in),
+                    t_ffin=_pack_ff_ln(tm.ff_in, tm.norm_in) if fold else _pack_ff(tm.ff_in, dev),
+                    t_attn1=_pack_attn_self_ln(tm.attn1, tm.norm1) if fold else _pack_attn_self(tm.attn1),
+                    t_attn2=_pack_attn_cross(tm.attn2),
+                    t_ff=_pack_ff_ln(tm.ff, tm.norm3) if fold else _pack_ff(tm.ff, dev),
+                    t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3), ln_fold=fold)
             elif isinstance(m, Downsample):
                 P[id(m)] = dict(w=pack.pack_conv3x3(m.op.weight), b=_f32(m.op.bias))
             elif isinstance(m, Upsample):
@@ -185,6 +230,128 @@ class _FrameGather:
         return 0
 
 
+class _RingAttention:
+    """Plan entry (called like a C-ABI launch): frame sequence-parallel 3D self-attention with the K/V exchange
+    OVERLAPPED with the attention itself (SURVEY 8e "ring variant").
+
+    Every rank holds q and [k | v] of its own frames.  The peers' [k | v] blocks travel on a second stream -- step s of
+    P - 1: send mine to rank + s, receive the block of rank - s (NCCL point-to-point over NVSwitch, straight into a
+    per-peer buffer of exactly that peer's size: no padded staging, no scatter copies) -- while the compute stream
+    attends to the blocks already here, local block first: one ``seva_attn_partial`` launch per block (fp32 result +
+    log-sum-exp of its scores), then ``seva_attn_merge`` (online-softmax merge of the P partial results).  Same
+    mathematics as one attention over the gathered keys; the exchange is hidden behind P - 1 of the P block attentions.
+    ``mode`` = "allgather": one all-gather on the second stream instead of the P - 1 steps (overlaps the local block only).
+    """
+    __name__ = "ring_attn3d"
+
+    def __init__(self, lib, shard: FrameShard, q, kvl, o, B, heads, S, C_, mode="ring"):
+        self.lib, self.shard, self.q, self.kvl, self.o = lib, shard, q, kvl, o
+        self.B, self.heads, self.S, self.C = B, heads, S, C_
+        self.mode = mode
+        dev, P = q.device, shard.size
+        self.Lq = shard.T_local * S
+        self.parts = torch.empty(P, B, self.Lq, C_, device=dev, dtype=F32)
+        self.lse = torch.empty(P, B, heads, self.Lq, device=dev, dtype=F32)
+        self.peer = [None if r == shard.rank else torch.empty(B, shard.counts[r] * S, 2 * C_, device=dev, dtype=BF16)
+                     for r in range(P)]
+        self.n_kernels = P + 1
+        self._events = None
+        st = shard._stage.get("ring_stream")
+        if st is None:
+            st = shard._stage["ring_stream"] = torch.cuda.Stream(device=dev)
+        self.comm = st
+
+    def start(self, stream=None) -> int:
+        """Enqueue the exchange on the second stream (plan entry placed right after the K/V projection, so that the
+        blocks travel while q is still being projected)."""
+        import torch.distributed as dist
+
+        sh, P, me = self.shard, self.shard.size, self.shard.rank
+        cur = torch.cuda.current_stream()
+        ready = torch.cuda.Event()
+        ready.record(cur)                      # kvl was produced on the compute stream
+        events = {}
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(ready)
+            if self.mode == "ring":
+                ranks = dist.get_process_group_ranks(sh.group)
+                for step in range(1, P):
+                    dst, src = (me + step) % P, (me - step) % P
+                    ops_ = [dist.P2POp(dist.isend, self.kvl, ranks[dst], group=sh.group),
+                            dist.P2POp(dist.irecv, self.peer[src], ranks[src], group=sh.group)]
+                    for req in dist.batch_isend_irecv(ops_):
+                        req.wait()
+                    events[src] = torch.cuda.Event()
+                    events[src].record(self.comm)
+            else:
+                dist.all_gather_into_tensor(self._gathered(), self._send_padded(), group=sh.group)
+                ev = torch.cuda.Event()
+                ev.record(self.comm)
+                events = {r: ev for r in range(P) if r != me}
+        self._events = events
+        return 0
+
+    def block(self, r):
+        """(tensor, keys, batch stride) of rank r's [k | v] block as this rank holds it."""
+        sh = self.shard
+        if r == sh.rank:
+            return self.kvl, self.Lq, self.Lq * 2 * self.C
+        if self.mode == "ring":
+            return self.peer[r], sh.counts[r] * self.S, sh.counts[r] * self.S * 2 * self.C
+        kv = self._gathered()[r]
+        return kv, sh.counts[r] * self.S, kv.stride(0)
+
+    def compute(self, stream, events=None) -> int:
+        """Local block first, then the peers' blocks in arrival order, then the merge."""
+        P, me = self.shard.size, self.shard.rank
+        cur = torch.cuda.current_stream()
+        for r in [me] + [(me - step) % P for step in range(1, P)]:
+            if events is not None and r != me:
+                cur.wait_event(events[r])
+            kv, Lk, bs = self.block(r)
+            rc = self.lib.seva_attn_partial(self.q.data_ptr(), kv.data_ptr(), kv.data_ptr() + 2 * self.C,
+                                            self.parts[r].data_ptr(), self.lse[r].data_ptr(), self.B, self.heads, self.Lq,
+                                            Lk, self.C, 2 * self.C, 2 * self.C, self.Lq * self.C, bs, bs, 0.125, stream)
+            if rc:
+                return rc
+        return self.lib.seva_attn_merge(self.parts.data_ptr(), self.lse.data_ptr(), self.o.data_ptr(), P, self.B, self.heads,
+                                        self.Lq, self.o.stride(0), self.Lq * self.o.stride(0), stream)
+
+    def __call__(self, stream) -> int:
+        if self._events is None:
+            self.start(stream)
+        events, self._events = self._events, None
+        return self.compute(stream, events)
+
+    # ---- all-gather variant: padded blocks (the frame split is uneven: T = 21 never divides) -----------------------
+    def _gathered(self):
+        sh = self.shard
+        key = ("ring_ag", self.B, max(sh.counts) * self.S, self.C)
+        st = sh._stage.get(key)
+        if st is None:
+            cmax = max(sh.counts) * self.S
+            st = sh._stage[key] = (torch.zeros(self.B, cmax, 2 * self.C, device=self.q.device, dtype=BF16),
+                                   torch.empty(sh.size, self.B, cmax, 2 * self.C, device=self.q.device, dtype=BF16))
+        return st[1]
+
+    def _send_padded(self):
+        self._gathered()
+        send = self.shard._stage[("ring_ag", self.B, max(self.shard.counts) * self.S, self.C)][0]
+        send[:, : self.Lq].copy_(self.kvl.view(self.B, self.Lq, 2 * self.C))
+        return send
+
+
+class _RingStart:
+    """Plan entry: begin a ``_RingAttention``'s K/V exchange (no kernel of ours)."""
+    __name__ = "ring_exchange_start"
+
+    def __init__(self, ring: _RingAttention):
+        self.ring = ring
+
+    def __call__(self, stream) -> int:
+        return self.ring.start(stream)
+
+
 class _SpaceExchange:
     """Plan entry (called like a C-ABI launch): all-to-all between the frame-sharded token layout
     [B, T_local, S, C] and the space-sharded layout [B, T_total, S_local, C].
@@ -263,6 +430,7 @@ class Engine:
         self.bufs: dict = {}
         self.n_launch = 0
         self.gemv_groups: dict = {}
+        self.gn_src: dict = {}   # (data_ptr, columns) of a GEMM output -> (partial-statistics buffer, rows per image)
         # time-mix attention under a frame shard: all-to-all to a space-sharded layout (default) or K/V all-gather
         # (measured at T=21: 8 ranks 26.4 vs 30.2 ms/step in favour of the all-to-all, 4 ranks a tie, 2 ranks 59.0 vs 56.7)
         env = os.environ.get("SEVA_TIMEMIX_A2A")
@@ -331,14 +499,24 @@ class Engine:
         (2*MAC for Linear/conv on unpadded pixels, 4*B*H*Lq*Lk*D for attention, activation bytes for norms)."""
         self.calls.append((fn, args))
         self.meta.append((fn.__name__, tag, float(flops), float(nbytes)))
-        if not isinstance(fn, (_FrameGather, _SpaceExchange)):  # collectives are NCCL's kernels, not ours
+        if isinstance(fn, _RingAttention):
+            self.n_launch += fn.n_kernels
+        elif not isinstance(fn, (_FrameGather, _SpaceExchange, _RingStart)):  # collectives are NCCL's kernels, not ours
             self.n_launch += 1
 
     # ---- op emitters (each appends exactly one kernel launch unless noted) ---------------------
     def gemm(self, A, W, out, *, bias=None, M=None, ntaps=1, tap_wp=0, rowbias=None, rowbias_rpi=0, residual=None,
              out_fp32=False, geglu=False, out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, Kc=None,
-             alg_rows=None, alg_k=None):
+             alg_rows=None, alg_k=None, gn_rpi=0, ln_rows=None, ln_in=None, ln_colsum=None, ln_eps=1e-5):
+        """``gn_rpi`` > 0: the epilogue also writes GroupNorm partial statistics of ``out`` (rows of M space per image);
+        ``ln_rows``: ... LayerNorm row partials of ``out``; ``ln_in`` / ``ln_colsum``: LayerNorm(A) folded in."""
         M = A.shape[0] if M is None else M
+        gn_part = None
+        if gn_rpi and FUSED_GN_STATS and not out_fp32 and W.shape[0] % 32 == 0:
+            gn_part = self.buf(f"gnp_{out.data_ptr()}_{W.shape[0]}", ops.gn_partial_floats(self.N, gn_rpi, W.shape[0]), 1, F32)
+            self.gn_src[(out.data_ptr(), W.shape[0])] = (gn_part, gn_rpi)
+        else:
+            self.gn_src.pop((out.data_ptr(), W.shape[0]), None)  # a stale record must not describe new contents
         g = ops.make_gemm(A_ptr=A.data_ptr(), lda=A.stride(0), a_rows=A.shape[0], W_ptr=W.data_ptr(),
                           ldw=W.stride(0), M=M, N=W.shape[0], Kc=A.shape[1] if Kc is None else Kc,
                           out_ptr=out.data_ptr(), ldo=out.stride(0), ntaps=ntaps, tap_wp=tap_wp,
@@ -347,28 +525,52 @@ class Engine:
                           residual_ptr=None if residual is None else residual.data_ptr(),
                           ldr=0 if residual is None else residual.stride(0), out_fp32=out_fp32, geglu=geglu,
                           out_map=out_map, H=H, Wd=Wd, mask_border=mask_border, Hp=Hp, Wp=Wp, bn=bn,
-                          reverse=self._dir(A, out))
-        self.keep += [g, A, W, out, bias, rowbias, residual]
+                          reverse=self._dir(A, out),
+                          gn_partial_ptr=None if gn_part is None else gn_part.data_ptr(), gn_rpi=gn_rpi,
+                          ln_rowstats_ptr=None if ln_rows is None else ln_rows.data_ptr(),
+                          ln_in_ptr=None if ln_in is None else ln_in.data_ptr(),
+                          ln_in_slots=0 if ln_in is None else ln_in.shape[0], ln_eps=ln_eps,
+                          ln_colsum_ptr=None if ln_colsum is None else ln_colsum.data_ptr())
+        self.keep += [g, A, W, out, bias, rowbias, residual, ln_rows, ln_in, ln_colsum]
         m_alg = M if alg_rows is None else alg_rows
         kk = (A.shape[1] if Kc is None else Kc) if alg_k is None else alg_k
         self.add(self.lib.seva_gemm_bf16, C.byref(g), flops=2.0 * m_alg * W.shape[0] * kk * ntaps,
                  tag=("conv3x3" if ntaps == 9 else ("geglu" if geglu else "linear")) + f" M{M} N{W.shape[0]} K{kk * ntaps}")
 
-    def conv3x3(self, x, l, W9, bias, out, *, rowbias=None, residual=None, out_fp32=False, alg_k=None):
+    def conv3x3(self, x, l, W9, bias, out, *, rowbias=None, residual=None, out_fp32=False, alg_k=None, stats=True):
         H, Wd = self.HW[l]
         self.gemm(x, W9, out, bias=bias, ntaps=9, tap_wp=Wd + 2, rowbias=rowbias, rowbias_rpi=(H + 2) * (Wd + 2),
                   residual=residual, out_fp32=out_fp32, mask_border=True, Hp=H + 2, Wp=Wd + 2,
-                  alg_rows=self.rows_c(l), alg_k=alg_k)
+                  alg_rows=self.rows_c(l), alg_k=alg_k, gn_rpi=(H + 2) * (Wd + 2) if stats and not out_fp32 else 0)
 
     def gn(self, x, l, C_, gamma, beta, eps, out, *, in_padded=True, out_padded=True, silu=False, dense=None,
            dense_w=None, dense_b=None):
         """GroupNorm: stats launch (+ memset inside) and apply launch."""
         H, Wd = self.HW[l]
         rpi = (H + 2) * (Wd + 2) if in_padded else H * Wd
+        act = 2.0 * self.N * H * Wd * C_
+        srcs = self._gn_sources(x, C_)
+        if srcs is not None:
+            # statistics came out of the producing GEMM epilogues: fold their partials (no pass over x)
+            gst = self.buf(f"gn_gstats_{C_}", self.N * 32 * 2, 1, F32)
+            (p0, c0, r0), (p1, c1, r1) = srcs[0], (srcs[1] if len(srcs) > 1 else (None, 0, 0))
+            self.add(self.lib.seva_groupnorm_finalize, p0.data_ptr(), c0, r0, None if p1 is None else p1.data_ptr(), c1, r1,
+                     self.N, 32, H * Wd, eps, gst.data_ptr(), nbytes=act / 8.0, tag=f"gn_finalize HW{H * Wd} C{C_}")
+            pa = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
+                                   sums_ptr=None, gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(),
+                                   n_img=self.N, H=H, Wd=Wd, Cc=C_, groups=32, eps=eps, in_padded=in_padded,
+                                   out_padded=out_padded, silu=silu,
+                                   dense_ptr=None if dense is None else dense.data_ptr(),
+                                   dense_w_ptr=None if dense_w is None else dense_w.data_ptr(),
+                                   dense_b_ptr=None if dense_b is None else dense_b.data_ptr(),
+                                   reverse=self._dir(x, out), gstats_ptr=gst.data_ptr())
+            self.keep += [pa, x, out, gamma, beta, dense, dense_w, dense_b, gst]
+            self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act,
+                     tag=f"gn_apply HW{H * Wd} C{C_} d{int(dense is not None)}")
+            return
         # one buffer per (rows, channels): its ticket words sit at a shape-dependent offset and must stay zero between
         # launches, so shapes never share a buffer (zero-initialised by ``buf``, self-resetting afterwards)
         sums = self.buf(f"gn_sums_{rpi}_{C_}", ops.gn_stats_floats(self.N, rpi, C_), 1, F32)
-        act = 2.0 * self.N * H * Wd * C_
         self.add(self.lib.seva_groupnorm_stats, x.data_ptr(), x.stride(0), self.N, rpi, C_, sums.data_ptr(),
                  int(self._dir(x)), nbytes=act, tag=f"gn_stats HW{H * Wd} C{C_}")
         pa = ops.make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
@@ -381,6 +583,20 @@ class Engine:
                                reverse=self._dir(x, out))
         self.keep += [pa, x, out, gamma, beta, dense, dense_w, dense_b]
         self.add(self.lib.seva_groupnorm_apply, C.byref(pa), nbytes=2.0 * act, tag=f"gn_apply HW{H * Wd} C{C_} d{int(dense is not None)}")
+
+    def _gn_sources(self, x, C_):
+        """[(partial, channels, rows per image)] of the one or two GEMM outputs (side by side along the channel axis)
+        that make up ``x``, or None when some part of it was not produced with statistics."""
+        got, ptr, left = [], x.data_ptr(), C_
+        while left > 0:
+            hit = next(((k, v) for k, v in self.gn_src.items() if k[0] == ptr and k[1] <= left), None)
+            if hit is None or len(got) == 2:
+                return None
+            (_, ncols), (part, rpi) = hit
+            got.append((part, ncols, rpi))
+            ptr += 2 * ncols
+            left -= ncols
+        return got
 
     def ln(self, x, nrm, out):
         self.add(self.lib.seva_layernorm, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0),
@@ -550,7 +766,7 @@ class Engine:
         self.add(self.lib.seva_im2col3x3_s2, x.data_ptr(), x.stride(0), col.data_ptr(), self.N, H, Wd, m.channels)
         self._touch_forward(x, col)
         self.keep += [x]
-        self.gemm(col, w["w"], out, bias=w["b"], out_map=1, H=Ho, Wd=Wo)
+        self.gemm(col, w["w"], out, bias=w["b"], out_map=1, H=Ho, Wd=Wo, gn_rpi=Ho * Wo)
 
     # Upsample.forward, layers.py:42-46
     def _up(self, m: Upsample, x, l, out):
@@ -573,14 +789,25 @@ class Engine:
         self.gemv(v, wa["wo"], wa["bo"], o, group="cross_o")
         return o
 
-    def _ff(self, x, nrm, ff, residual, out, l, C_in, tag):
+    def _rows(self, l, C_):
+        """LayerNorm row-partial buffer of level ``l`` ([slots, rows, 2] fp32): written by the epilogue of the GEMM
+        that produces a LayerNorm input and read by the GEMM the LayerNorm is folded into, back to back."""
+        return self.buf(f"tk_rows_{l}", ops.ln_slots(C_) * self.rows_c(l) * 2, 1, F32).view(ops.ln_slots(C_), self.rows_c(l), 2)
+
+    def _ff(self, x, nrm, ff, residual, out, l, C_in, tag, x_rows=None, out_rows=None):
+        """FeedForward(LayerNorm(x)) + residual.  ``x_rows``: row statistics of x from its producer (the LayerNorm is
+        then folded into the GEGLU projection); ``out_rows``: have the down projection write row statistics of out."""
         rc = x.shape[0]
-        a = self.buf(f"tk_ln_{l}", rc, C_in)
-        self.ln(x, nrm, a)
         inner = ff["w1"].shape[0] // 2
         g = self.buf(f"tk_g_{l}", rc, inner)
-        self.gemm(a, ff["w1"], g, bias=ff["b1"], geglu=True, bn=ff["bn1"])
-        self.gemm(g, ff["w2"], out, bias=ff["b2"], residual=residual)
+        if x_rows is not None:
+            self.gemm(x, ff["w1"], g, bias=ff["b1"], geglu=True, bn=ff["bn1"], ln_in=x_rows, ln_colsum=ff["cs1"],
+                      ln_eps=ff["eps"])
+        else:
+            a = self.buf(f"tk_ln_{l}", rc, C_in)
+            self.ln(x, nrm, a)
+            self.gemm(a, ff["w1"], g, bias=ff["b1"], geglu=True, bn=ff["bn1"])
+        self.gemm(g, ff["w2"], out, bias=ff["b2"], residual=residual, ln_rows=out_rows)
 
     # MultiviewTransformer.forward, transformer.py:215-247
     def _mvt(self, m: MultiviewTransformer, x, l, out):
@@ -597,26 +824,47 @@ class Engine:
         xn = self.buf(f"tk_xn_{l}", rc, C_)
         self.gn(x, l, C_, w["gn"]["g"], w["gn"]["b"], w["gn"]["eps"], xn, out_padded=False)
         x0 = self.buf(f"tk_x0_{l}", rc, C_)
-        self.gemm(xn, w["win"], x0, bias=w["bin"])
+        # LayerNorm -> Linear pairs: the producer of the LayerNorm input writes per-row (sum, sum of squares) partials
+        # in its epilogue and the consuming projection applies mean / rstd in ITS epilogue (gamma / beta folded into
+        # the packed weights), so no LayerNorm pass touches HBM.  ``rows`` is None when folding is off for this width.
+        fold = w["ln_fold"]
+        rows = self._rows(l, C_) if fold else None
+        self.gemm(xn, w["win"], x0, bias=w["bin"], ln_rows=rows)
 
         # ---- spatial block (TransformerBlock.forward, transformer.py:106-110)
         a = self.buf(f"tk_ln_{l}", rc, C_)
-        self.ln(x0, w["s_n1"], a)
+        if not fold:
+            self.ln(x0, w["s_n1"], a)
+        qkv_in = dict(A=x0, ln=dict(ln_in=rows, ln_eps=w["s_attn1"]["eps"])) if fold else dict(A=a, ln={})
         qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
         o = self.buf(f"tk_o_{l}", rc, C_)
         bat, Lseq = (B, T * S) if is3d else (self.N, S)
         sh = self.shard
         if is3d and sh is not None:
             # frame sequence-parallel 3D attention: local queries against the keys / values of all Tk frames
-            q, kvl, kvf = self._split_qkv(a, w["s_attn1"]["wqkv"], l, C_, S)
+            ring = os.environ.get("SEVA_RING", "ring")   # ring | allgather (both overlapped) | off (blocking gather)
             Lk = self.Tk * S
-            self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
-                     heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
-                     Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
-                     tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
-            self._touch_forward(q, kvf, o)
+            if ring != "off":
+                box = {}
+
+                def after_kv(q_, kvl_):
+                    box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, C_, mode=ring)
+                    self.add(_RingStart(box["ring"]), tag="start")
+
+                q, kvl, _ = self._split_qkv(qkv_in, w["s_attn1"], l, C_, S, gather=False, after_kv=after_kv)
+                self.add(box["ring"],
+                         flops=4.0 * bat * heads * Lseq * Lk * 64, nbytes=2.0 * bat * Lk * 2 * C_,
+                         tag=f"attn3d+exchange B{bat} H{heads} Lq{Lseq} Lk{Lk} {ring}")
+                self._touch_forward(q, o)
+            else:
+                q, kvl, kvf = self._split_qkv(qkv_in, w["s_attn1"], l, C_, S)
+                self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
+                         heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
+                         Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
+                         tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
+                self._touch_forward(q, kvf, o)
         else:
-            self.gemm(a, w["s_attn1"]["wqkv"], qkv)
+            self._qkv(qkv_in, w["s_attn1"], slice(None), qkv)
             ld = qkv.stride(0)
             base = qkv.data_ptr()
             self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
@@ -627,23 +875,26 @@ class Engine:
         x1 = self.buf(f"tk_x1_{l}", rc, C_)
         if self.L == 1:
             xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
-            self.gemm(o, w["s_attn1"]["wo"], x1, bias=w["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq)
+            self.gemm(o, w["s_attn1"]["wo"], x1, bias=w["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq,
+                      ln_rows=rows)
         else:
             x1a = self.buf(f"tk_x1a_{l}", rc, C_)
             self.gemm(o, w["s_attn1"]["wo"], x1a, bias=w["s_attn1"]["bo"], residual=x0)
             self._cross_general(w["s_attn2"], w["s_n2"], x1a, x1, l, C_, heads, bat, Lseq,
-                                self.ctx0_in if is3d else self.ctx_in)
+                                self.ctx0_in if is3d else self.ctx_in, out_rows=rows)
         x2 = self.buf(f"tk_x2_{l}", rc, C_)
-        self._ff(x1, w["s_n3"], w["s_ff"], x1, x2, l, C_, "s")
+        self._ff(x1, w["s_n3"], w["s_ff"], x1, x2, l, C_, "s", x_rows=rows, out_rows=rows)
 
         # ---- time-mix block (TransformerBlockTimeMix.forward, transformer.py:145-155), tokens stay (b t) s
         y1 = self.buf(f"tk_y1_{l}", rc, C_)
-        self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin")
-        self.ln(y1, w["t_n1"], a)
+        self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin", x_rows=rows, out_rows=rows)
+        if not fold:
+            self.ln(y1, w["t_n1"], a)
+        qkv_in = dict(A=y1, ln=dict(ln_in=rows, ln_eps=w["t_attn1"]["eps"])) if fold else dict(A=a, ln={})
         if sh is not None and self.tm_a2a and S >= sh.size:
             sa, sb = sh.space_parts(S)[sh.rank]
             S_me = sb - sa
-            self.gemm(a, w["t_attn1"]["wqkv"], qkv)
+            self._qkv(qkv_in, w["t_attn1"], slice(None), qkv)
             qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * C_)
             o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, C_)
             self.add(_SpaceExchange(sh, True, qkv, qkv_sp, B, S), nbytes=2.0 * (qkv.numel() + qkv_sp.numel()),
@@ -655,14 +906,14 @@ class Engine:
                      tag=f"to_frames rows{rc} C{C_}")
             self._touch_forward(qkv, o)
         elif sh is not None:
-            q, kvl, kvf = self._split_qkv(a, w["t_attn1"]["wqkv"], l, C_, S)
+            q, kvl, kvf = self._split_qkv(qkv_in, w["t_attn1"], l, C_, S)
             self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
                      o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
                      flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
                      tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
             self._touch_forward(q, kvf, o)
         else:
-            self.gemm(a, w["t_attn1"]["wqkv"], qkv)
+            self._qkv(qkv_in, w["t_attn1"], slice(None), qkv)
             self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
                      o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
                      tag=f"timemix BS{B * S} H{heads}")
@@ -671,27 +922,48 @@ class Engine:
         if self.L == 1:
             xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
             self.gemm(o, w["t_attn1"]["wo"], y2, bias=w["t_attn1"]["bo"], residual=y1, rowbias=xr,
-                      rowbias_rpi=T * S)
+                      rowbias_rpi=T * S, ln_rows=rows)
         else:
-            raise SevaB200Error("time-mix cross-attention with more than one context token is not implemented")
+            # time_context = context[::T] repeated over the positions (transformer.py:222-226): every token of batch
+            # element b attends to the same L context tokens, and cross-attention is per query token, so the (b t) s
+            # token order needs no transpose: batch = B, T * S queries each
+            y2a = self.buf(f"tk_x1a_{l}", rc, C_)
+            self.gemm(o, w["t_attn1"]["wo"], y2a, bias=w["t_attn1"]["bo"], residual=y1)
+            self._cross_general(w["t_attn2"], w["t_n2"], y2a, y2, l, C_, heads, B, T * S, self.ctx0_in, out_rows=rows)
         x3 = self.buf(f"tk_x3_{l}", rc, C_)
         # x = x_spatial + ff(norm3(y2)): SkipConnect (transformer.py:158-165) folded into the residual
-        self._ff(y2, w["t_n3"], w["t_ff"], x2, x3, l, C_, "t")
-        # proj_out + input residual, written back to the zero-bordered layout (transformer.py:244-247)
-        self.gemm(x3, w["wout"], out, bias=w["bout"], residual=x, out_map=1, H=H, Wd=Wd)
+        self._ff(y2, w["t_n3"], w["t_ff"], x2, x3, l, C_, "t", x_rows=rows)
+        # proj_out + input residual, written back to the zero-bordered layout (transformer.py:244-247); its epilogue
+        # also leaves the GroupNorm partials of the block output for the next ResBlock
+        self.gemm(x3, w["wout"], out, bias=w["bout"], residual=x, out_map=1, H=H, Wd=Wd, gn_rpi=S)
 
-    def _split_qkv(self, a, wqkv, l, C_, S):
-        """Frame-sharded self-attention input: q for the local frames, [k | v] gathered over the frame group."""
-        rc = a.shape[0]
+    def _qkv(self, src, wa, rows_sel, out):
+        """Rows ``rows_sel`` of the fused q|k|v projection of ``src['A']`` (the LayerNorm output, or the LayerNorm
+        INPUT with its row statistics when the LayerNorm is folded into this projection)."""
+        if src["ln"]:
+            self.gemm(src["A"], wa["wqkv"][rows_sel], out, bias=wa["bqkv"][rows_sel], ln_colsum=wa["csqkv"][rows_sel],
+                      **src["ln"])
+        else:
+            self.gemm(src["A"], wa["wqkv"][rows_sel], out)
+
+    def _split_qkv(self, src, wa, l, C_, S, gather=True, after_kv=None):
+        """Frame-sharded self-attention input: q for the local frames, [k | v] gathered over the frame group
+        (``gather=False``: only the local [k | v]; the caller exchanges it itself).  K/V are projected first so that
+        an overlapped exchange can start while q is still being projected."""
+        rc = src["A"].shape[0]
         q = self.buf(f"tk_q_{l}", rc, C_)
         kvl = self.buf(f"tk_kvl_{l}", rc, 2 * C_)
+        self._qkv(src, wa, slice(C_, None), kvl)
+        if after_kv is not None:
+            after_kv(q, kvl)
+        self._qkv(src, wa, slice(0, C_), q)
+        if not gather:
+            return q, kvl, None
         kvf = self.buf(f"tk_kvf_{l}", self.B * self.Tk * S, 2 * C_)
-        self.gemm(a, wqkv[:C_], q)
-        self.gemm(a, wqkv[C_:], kvl)
         self.add(_FrameGather(self.shard, kvf, kvl, self.B, S), nbytes=2.0 * kvf.numel(), tag=f"kv rows{kvf.shape[0]} C{2 * C_}")
         return q, kvl, kvf
 
-    def _cross_general(self, wa, nrm, xin, xout, l, C_, heads, bat, Lseq, ctx):
+    def _cross_general(self, wa, nrm, xin, xout, l, C_, heads, bat, Lseq, ctx, out_rows=None):
         """attn2 with Lk > 1 context tokens: LN -> q, k/v from context -> flash attention -> to_out + residual."""
         rc = xin.shape[0]
         a = self.buf(f"tk_ln_{l}", rc, C_)
@@ -711,7 +983,7 @@ class Engine:
                  self.L, C_, C_, C_, C_, Lseq * C_, self.L * C_, self.L * C_, Lseq * C_, 0.125,
                  flops=4.0 * bat * heads * Lseq * self.L * 64, tag="attn_cross")
         self._touch_forward(q, o)
-        self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin)
+        self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin, ln_rows=out_rows)
 
     # ---- execution ------------------------------------------------------------------------------
     def cond_current(self, epoch) -> bool:

@@ -43,7 +43,9 @@ def pick_bn(N: int, geglu: bool = False) -> int:
 # ------------------------------------------------------------------------------------------------
 def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1, tap_wp=0, bias_ptr=None,
               rowbias_ptr=None, rowbias_rpi=0, residual_ptr=None, ldr=0, out_fp32=False, geglu=False,
-              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, cluster=0, reverse=False) -> SevaGemm:
+              out_map=0, H=0, Wd=0, mask_border=False, Hp=0, Wp=0, bn=0, cluster=0, reverse=False,
+              gn_partial_ptr=None, gn_rpi=0, ln_rowstats_ptr=None, ln_in_ptr=None, ln_in_slots=0, ln_eps=1e-5,
+              ln_colsum_ptr=None) -> SevaGemm:
     g = SevaGemm()
     g.A, g.lda, g.a_rows = A_ptr, lda, a_rows
     g.W, g.ldw = W_ptr, ldw
@@ -54,7 +56,33 @@ def make_gemm(*, A_ptr, lda, a_rows, W_ptr, ldw, M, N, Kc, out_ptr, ldo, ntaps=1
     g.out_fp32, g.geglu, g.out_map, g.H, g.Wd = int(out_fp32), int(geglu), out_map, H, Wd
     g.mask_border, g.Hp, g.Wp, g.bn, g.cluster = int(mask_border), Hp, Wp, bn, cluster
     g.reverse = int(reverse)
+    g.gn_partial, g.gn_rpi, g.gn_slots = gn_partial_ptr, gn_rpi, ((gn_rpi + 31) // 32 + 1) if gn_partial_ptr else 0
+    g.ln_rowstats = ln_rowstats_ptr
+    g.ln_in_stats, g.ln_in_slots, g.ln_eps, g.ln_colsum = ln_in_ptr, ln_in_slots, ln_eps, ln_colsum_ptr
     return g
+
+
+def ln_slots(N: int, bn: int = 0) -> int:
+    """Row-statistic slots a GEMM with N output columns writes per row (SevaGemm.ln_rowstats)."""
+    return _lib.load().seva_gemm_ln_slots(N, bn)
+
+
+def gn_partial_floats(n_img: int, rpi: int, Cc: int) -> int:
+    n = _lib.load().seva_groupnorm_partial_floats(n_img, rpi, Cc)
+    if n < 0:
+        raise _lib.SevaB200Error(f"seva_groupnorm_partial_floats({n_img}, {rpi}, {Cc}) failed")
+    return int(n)
+
+
+def groupnorm_finalize(part0: torch.Tensor, C0: int, rpi0: int, n_img: int, pixels: int, eps: float, *, groups: int = 32,
+                       part1: torch.Tensor | None = None, C1: int = 0, rpi1: int = 0,
+                       out: torch.Tensor | None = None) -> torch.Tensor:
+    """Fold GEMM-epilogue partials into gstats [n_img, groups, 2] = (mean, rstd)."""
+    if out is None:
+        out = torch.empty((n_img, groups, 2), device=part0.device, dtype=torch.float32)
+    check(_lib.load().seva_groupnorm_finalize(part0.data_ptr(), C0, rpi0, _p(part1), C1, rpi1, n_img, groups, pixels,
+                                              eps, out.data_ptr(), _stream()), "seva_groupnorm_finalize")
+    return out
 
 
 def run_gemm(g: SevaGemm) -> None:
@@ -64,8 +92,12 @@ def run_gemm(g: SevaGemm) -> None:
 def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *, out: torch.Tensor | None = None,
            residual: torch.Tensor | None = None, rowbias: torch.Tensor | None = None, rowbias_rpi: int = 0,
            geglu: bool = False, out_fp32: bool = False, bn: int = 0, cluster: int = 0,
-           reverse: bool = False) -> torch.Tensor:
-    """out = A @ W.T (+bias) (+rowbias[row // rpi]) (+residual); A [M,K] bf16, W [N,K] bf16 (row strides free)."""
+           reverse: bool = False, gn_partial: torch.Tensor | None = None, gn_rpi: int = 0,
+           ln_rowstats: torch.Tensor | None = None, ln_in: torch.Tensor | None = None, ln_eps: float = 1e-5,
+           ln_colsum: torch.Tensor | None = None) -> torch.Tensor:
+    """out = A @ W.T (+bias) (+rowbias[row // rpi]) (+residual); A [M,K] bf16, W [N,K] bf16 (row strides free).
+    ``gn_partial`` / ``ln_rowstats``: statistics of the output for a following GroupNorm / LayerNorm;
+    ``ln_in`` ([slots, M, 2] from the producer of A) + ``ln_colsum``: LayerNorm(A) folded into this GEMM."""
     _req(A, torch.bfloat16, "A"), _req(W, torch.bfloat16, "W")
     M, K = A.shape
     N = W.shape[0]
@@ -76,7 +108,9 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *
                   Kc=K, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias), rowbias_ptr=_p(rowbias),
                   rowbias_rpi=rowbias_rpi, residual_ptr=_p(residual),
                   ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, geglu=geglu, bn=bn,
-                  cluster=cluster, reverse=reverse)
+                  cluster=cluster, reverse=reverse, gn_partial_ptr=_p(gn_partial), gn_rpi=gn_rpi,
+                  ln_rowstats_ptr=_p(ln_rowstats), ln_in_ptr=_p(ln_in), ln_in_slots=0 if ln_in is None else ln_in.shape[0],
+                  ln_eps=ln_eps, ln_colsum_ptr=_p(ln_colsum))
     run_gemm(g)
     return out
 
@@ -84,7 +118,7 @@ def linear(A: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None = None, *
 def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None, N_img: int, H: int, Wd: int, *,
                    out: torch.Tensor | None = None, residual: torch.Tensor | None = None,
                    rowbias: torch.Tensor | None = None, out_fp32: bool = False, bn: int = 0,
-                   cluster: int = 0, reverse: bool = False) -> torch.Tensor:
+                   cluster: int = 0, reverse: bool = False, gn_partial: torch.Tensor | None = None) -> torch.Tensor:
     """3x3/s1/p1 conv on a zero-bordered flat image x [N_img*(H+2)*(Wd+2), Cin]; W9 [Cout, 9*Cin] tap-major."""
     _req(x, torch.bfloat16, "x"), _req(W9, torch.bfloat16, "W9")
     rows, Cin = x.shape
@@ -97,7 +131,7 @@ def conv3x3_padded(x: torch.Tensor, W9: torch.Tensor, bias: torch.Tensor | None,
                   N=Cout, Kc=Cin, ntaps=9, tap_wp=Wp, out_ptr=out.data_ptr(), ldo=out.stride(0), bias_ptr=_p(bias),
                   rowbias_ptr=_p(rowbias), rowbias_rpi=Hp * Wp, residual_ptr=_p(residual),
                   ldr=residual.stride(0) if residual is not None else 0, out_fp32=out_fp32, mask_border=True,
-                  Hp=Hp, Wp=Wp, bn=bn, cluster=cluster, reverse=reverse)
+                  Hp=Hp, Wp=Wp, bn=bn, cluster=cluster, reverse=reverse, gn_partial_ptr=_p(gn_partial), gn_rpi=Hp * Wp)
     run_gemm(g)
     return out
 
@@ -133,6 +167,38 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int,
     check(_lib.load().seva_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), B, heads, Lq, Lk,
                                     q.stride(1), k.stride(1), v.stride(1), out.stride(1), q.stride(0), k.stride(0),
                                     v.stride(0), out.stride(0), 1.0 / math.sqrt(64.0), _stream()), "seva_attn_fwd")
+    return out
+
+
+def attention_partial(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, out: torch.Tensor | None = None,
+                      lse: torch.Tensor | None = None):
+    """Attention of q [B, Lq, heads*64] over ONE key block k / v [B, Lk, heads*64]: (fp32 result [B, Lq, heads*64],
+    base-2 log-sum-exp [B, heads, Lq]) for ``attention_merge``."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _req(t, torch.bfloat16, n)
+        assert t.stride(2) == 1
+    B, Lq, Cc = q.shape
+    Lk = k.shape[1]
+    if out is None:
+        out = torch.empty((B, Lq, Cc), device=q.device, dtype=torch.float32)
+    if lse is None:
+        lse = torch.empty((B, heads, Lq), device=q.device, dtype=torch.float32)
+    check(_lib.load().seva_attn_partial(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(), B, heads,
+                                        Lq, Lk, q.stride(1), k.stride(1), v.stride(1), q.stride(0), k.stride(0),
+                                        v.stride(0), 1.0 / math.sqrt(64.0), _stream()), "seva_attn_partial")
+    return out, lse
+
+
+def attention_merge(partials: torch.Tensor, lse: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """partials [P, B, Lq, C] fp32, lse [P, B, heads, Lq] fp32 -> bf16 [B, Lq, C]."""
+    _req(partials, torch.float32, "partials"), _req(lse, torch.float32, "lse")
+    assert partials.is_contiguous() and lse.is_contiguous()
+    P, B, Lq, Cc = partials.shape
+    heads = lse.shape[2]
+    if out is None:
+        out = torch.empty((B, Lq, Cc), device=partials.device, dtype=torch.bfloat16)
+    check(_lib.load().seva_attn_merge(partials.data_ptr(), lse.data_ptr(), out.data_ptr(), P, B, heads, Lq, out.stride(1),
+                                      out.stride(0), _stream()), "seva_attn_merge")
     return out
 
 
@@ -189,7 +255,7 @@ def groupnorm_stats(x: torch.Tensor, n_img: int, rpi: int, Cc: int, sums: torch.
 
 def make_gn_apply(*, x_ptr, ldx, y_ptr, ldy, sums_ptr, gamma_ptr, beta_ptr, n_img, H, Wd, Cc, groups, eps,
                   in_padded, out_padded, silu, dense_ptr=None, dense_w_ptr=None, dense_b_ptr=None,
-                  reverse=False) -> SevaGNApply:
+                  reverse=False, gstats_ptr=None) -> SevaGNApply:
     p = SevaGNApply()
     p.x, p.ldx, p.y, p.ldy = x_ptr, ldx, y_ptr, ldy
     p.sums, p.gamma, p.beta = sums_ptr, gamma_ptr, beta_ptr
@@ -197,6 +263,7 @@ def make_gn_apply(*, x_ptr, ldx, y_ptr, ldy, sums_ptr, gamma_ptr, beta_ptr, n_im
     p.eps, p.in_padded, p.out_padded, p.silu = eps, int(in_padded), int(out_padded), int(silu)
     p.dense, p.dense_w, p.dense_b = dense_ptr, dense_w_ptr, dense_b_ptr
     p.reverse = int(reverse)
+    p.gstats = gstats_ptr
     return p
 
 
@@ -206,21 +273,23 @@ def run_gn_apply(p: SevaGNApply) -> None:
 
 def groupnorm(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, n_img: int, H: int, Wd: int, *, groups=32,
               eps=1e-5, in_padded=True, out_padded=True, silu=False, dense=None, dense_w=None, dense_b=None,
-              out: torch.Tensor | None = None, reverse: bool = False) -> torch.Tensor:
-    """GroupNorm (+SiLU, +dense modulation) of a channels-last image batch (two launches: stats, apply)."""
+              out: torch.Tensor | None = None, reverse: bool = False,
+              gstats: torch.Tensor | None = None) -> torch.Tensor:
+    """GroupNorm (+SiLU, +dense modulation) of a channels-last image batch (two launches: stats, apply; with
+    ``gstats`` from ``groupnorm_finalize`` only the apply launch)."""
     _req(x, torch.bfloat16, "x")
     Cc = x.shape[1]
     rpi_in = (H + 2) * (Wd + 2) if in_padded else H * Wd
     rpi_out = (H + 2) * (Wd + 2) if out_padded else H * Wd
     assert x.shape[0] == n_img * rpi_in
-    sums = groupnorm_stats(x, n_img, rpi_in, Cc, reverse=reverse)
+    sums = None if gstats is not None else groupnorm_stats(x, n_img, rpi_in, Cc, reverse=reverse)
     if out is None:
         out = torch.empty((n_img * rpi_out, Cc), device=x.device, dtype=torch.bfloat16)
     p = make_gn_apply(x_ptr=x.data_ptr(), ldx=x.stride(0), y_ptr=out.data_ptr(), ldy=out.stride(0),
-                      sums_ptr=sums.data_ptr(), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(), n_img=n_img,
+                      sums_ptr=_p(sums), gamma_ptr=gamma.data_ptr(), beta_ptr=beta.data_ptr(), n_img=n_img,
                       H=H, Wd=Wd, Cc=Cc, groups=groups, eps=eps, in_padded=in_padded, out_padded=out_padded,
                       silu=silu, dense_ptr=_p(dense), dense_w_ptr=_p(dense_w), dense_b_ptr=_p(dense_b),
-                      reverse=not reverse)
+                      reverse=not reverse, gstats_ptr=_p(gstats))
     run_gn_apply(p)
     return out
 

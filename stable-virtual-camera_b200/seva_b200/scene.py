@@ -208,6 +208,23 @@ def sample_window(model, denoiser, sampler, win: PL.Window, rows: dict, all_c2ws
     return out.detach().cpu()[win.test_sels]
 
 
+def window_noise_seed(base_seed: int, pass_index: int, window_index: int) -> int:
+    """Seed of the per-step noise stream (``torch.randn_like`` in ``sampler_step``, sampling.py:361) of one window.
+    The reference draws it from cuda:0's global Philox stream sequentially over the windows; here every window gets
+    its own stream derived from (scene seed, pass, window), so a window's latents do not depend on which rank samples
+    it or on what was sampled before it: an N-rank run returns the 1-rank run's latents."""
+    return (int(base_seed) * 1000003 + pass_index * 10007 + window_index * 101 + 12345) % (2**63 - 1)
+
+
+def _seed_step_noise(device, seed: int) -> None:
+    dev = torch.device(device)
+    if dev.type == "cuda":
+        with torch.cuda.device(dev):
+            torch.cuda.manual_seed(seed)
+    else:
+        torch.manual_seed(seed)
+
+
 def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Callable, codec: Codec | None = None,
               where: Rank | None = None, generator: torch.Generator | None = None, camera_scale: float = 2.0,
               device="cuda", sample_fn: Callable | None = None) -> torch.Tensor:
@@ -228,6 +245,7 @@ def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Call
                   K=scene.input_Ks.float().cpu())
     two_pass = len(plan.passes) == 2
     result = None
+    base_seed = generator.initial_seed() if generator is not None else torch.initial_seed()
     for pi, ps in enumerate(plan.passes):
         last = pi == len(plan.passes) - 1
         if two_pass and not last:   # anchors
@@ -257,6 +275,7 @@ def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Call
                 else:
                     s = dict(img=torch.cat([inputs["img"]] + gen_img), c2w=torch.cat([inputs["c2w"], table["c2w"][gen_idx]]),
                              K=torch.cat([inputs["K"], table["K"][gen_idx]]))
+                _seed_step_noise(device, window_noise_seed(base_seed, pi, k))
                 done[k] = sample_fn(model, denoiser, sampler, win, _window_inputs(win, s, table), all_c2ws, noise[k],
                                     ps.cfg, codec, camera_scale, device)
                 gen_img.append(done[k])
@@ -270,6 +289,7 @@ def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Call
             local = {}
             for k in mine:
                 win = ps.windows[k]
+                _seed_step_noise(device, window_noise_seed(base_seed, pi, k))
                 out = sample_fn(model, denoiser, sampler, win, _window_inputs(win, src if (two_pass and last) else inputs, table),
                                 all_c2ws, noise[k], ps.cfg, codec, camera_scale, device)
                 pad = torch.zeros((ps.T,) + tuple(out.shape[1:]), dtype=out.dtype)  # equal shapes for the gather

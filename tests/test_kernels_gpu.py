@@ -488,3 +488,177 @@ def test_groupnorm_stats_buffer_reuse_is_deterministic(ops):
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
     ref = torch.stack([x.float().view(n_img, rpi, Cc).sum(1), (x.float() ** 2).view(n_img, rpi, Cc).sum(1)], -1)
     assert rel_l2(outs[0].view(n_img, Cc, 2), ref) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------------
+# statistics fused into the producing GEMM's epilogue (GroupNorm partials, LayerNorm row sums) and
+# LayerNorm folded into the consuming GEMM
+# ---------------------------------------------------------------------------------------------------
+def _gn_ref_stats(x_nchw, groups, eps):
+    n, c = x_nchw.shape[:2]
+    xg = x_nchw.double().reshape(n, groups, -1)
+    mean = xg.mean(-1)
+    var = xg.var(-1, unbiased=False)
+    return torch.stack([mean, 1.0 / torch.sqrt(var + eps)], -1).float()
+
+
+@pytest.mark.parametrize("cluster", [1, 2])
+@pytest.mark.parametrize("n_img,H,Wd,Cin,Cout,residual", [(3, 18, 18, 64, 320, True), (2, 9, 9, 128, 640, False),
+                                                          (5, 2, 2, 64, 64, True), (2, 36, 20, 64, 960, False)])
+def test_conv_epilogue_groupnorm_partials(ops, cluster, n_img, H, Wd, Cin, Cout, residual):
+    """conv3x3 writes per-32-row-block channel partials of its own output; finalize folds them to (mean, rstd) per
+    (image, group) -- compared with group statistics of the stored bf16 output, and GroupNorm through ``gstats`` with
+    the two-launch path.  Images smaller than a 32-row block (2x2) and blocks straddling images are covered."""
+    from seva_b200 import pack
+
+    g = torch.Generator(device="cuda").manual_seed(H * Cout + cluster)
+    x = bf(torch.randn(n_img, Cin, H, Wd, device="cuda", generator=g))
+    w = torch.randn(Cout, Cin, 3, 3, device="cuda", generator=g) / math.sqrt(9 * Cin)
+    b = torch.randn(Cout, device="cuda", generator=g) * 3.0  # a mean well away from zero
+    xp = F.pad(x.permute(0, 2, 3, 1), (0, 0, 1, 1, 1, 1)).reshape(-1, Cin).contiguous()
+    rpi = (H + 2) * (Wd + 2)
+    res = None
+    if residual:
+        res = F.pad(bf(torch.randn(n_img, H, Wd, Cout, device="cuda", generator=g)), (0, 0, 1, 1, 1, 1)).reshape(-1, Cout).contiguous()
+    part = torch.full((ops.gn_partial_floats(n_img, rpi, Cout),), float("nan"), device="cuda")
+    out = ops.conv3x3_padded(xp, pack.pack_conv3x3(w), b, n_img, H, Wd, residual=res, cluster=cluster, gn_partial=part)
+    plain = ops.conv3x3_padded(xp, pack.pack_conv3x3(w), b, n_img, H, Wd, residual=res, cluster=cluster)
+    assert torch.equal(out, plain)  # the statistics do not perturb the output
+    gst = ops.groupnorm_finalize(part, Cout, rpi, n_img, H * Wd, 1e-5)
+    o = out.reshape(n_img, H + 2, Wd + 2, Cout)[:, 1:-1, 1:-1].permute(0, 3, 1, 2)
+    ref = _gn_ref_stats(o.float(), 32, 1e-5)
+    tol = 2e-3 if residual else 1e-5  # residual path: statistics of the fp32 values before the bf16 rounding
+    assert (gst[..., 0] - ref[..., 0]).abs().max().item() < tol * (1 + ref[..., 0].abs().max().item())
+    assert ((gst[..., 1] - ref[..., 1]).abs() / ref[..., 1]).max().item() < max(tol, 1e-4)
+    gamma = torch.randn(Cout, device="cuda", generator=g)
+    beta = torch.randn(Cout, device="cuda", generator=g)
+    y_fused = ops.groupnorm(out, gamma, beta, n_img, H, Wd, silu=True, gstats=gst)
+    y_two = ops.groupnorm(out, gamma, beta, n_img, H, Wd, silu=True)
+    assert rel_l2(y_fused, y_two) < 2e-3
+    assert torch.equal(ops.groupnorm_finalize(part, Cout, rpi, n_img, H * Wd, 1e-5), gst)  # deterministic
+
+
+def test_gemm_epilogue_groupnorm_partials_two_sources(ops):
+    """The decoder's virtual skip concat: two producers with DIFFERENT row spaces (a token GEMM scattered into the
+    zero-bordered layout, out_map = 1, and a conv over zero-bordered rows) write column slices of one buffer; 30-channel
+    groups straddle the 640 | 320 seam."""
+    from seva_b200 import _lib, pack
+
+    g = torch.Generator(device="cuda").manual_seed(77)
+    n_img, H, Wd, C0, C1 = 3, 12, 10, 640, 320
+    rp, rc = (H + 2) * (Wd + 2), H * Wd
+    cat = torch.zeros(n_img * rp, C0 + C1, device="cuda", dtype=torch.bfloat16)
+    # source 0: token GEMM -> padded rows (out_map = 1), statistics in compact row space
+    A = bf(torch.randn(n_img * rc, 256, device="cuda", generator=g))
+    W0 = bf(torch.randn(C0, 256, device="cuda", generator=g) / 16)
+    b0 = torch.randn(C0, device="cuda", generator=g)
+    part0 = torch.zeros(ops.gn_partial_floats(n_img, rc, C0), device="cuda")
+    o0 = cat[:, :C0]
+    gd = ops.make_gemm(A_ptr=A.data_ptr(), lda=A.stride(0), a_rows=A.shape[0], W_ptr=W0.data_ptr(), ldw=W0.stride(0),
+                       M=A.shape[0], N=C0, Kc=256, out_ptr=o0.data_ptr(), ldo=o0.stride(0), bias_ptr=b0.data_ptr(),
+                       out_map=1, H=H, Wd=Wd, gn_partial_ptr=part0.data_ptr(), gn_rpi=rc)
+    ops.run_gemm(gd)
+    # source 1: conv over zero-bordered rows
+    x = bf(torch.randn(n_img, 64, H, Wd, device="cuda", generator=g))
+    w = torch.randn(C1, 64, 3, 3, device="cuda", generator=g) / 24
+    xp = F.pad(x.permute(0, 2, 3, 1), (0, 0, 1, 1, 1, 1)).reshape(-1, 64).contiguous()
+    part1 = torch.zeros(ops.gn_partial_floats(n_img, rp, C1), device="cuda")
+    ops.conv3x3_padded(xp, pack.pack_conv3x3(w), None, n_img, H, Wd, out=cat[:, C0:], gn_partial=part1)
+    gst = ops.groupnorm_finalize(part0, C0, rc, n_img, rc, 1e-5, part1=part1, C1=C1, rpi1=rp)
+    o = cat.reshape(n_img, H + 2, Wd + 2, C0 + C1)[:, 1:-1, 1:-1].permute(0, 3, 1, 2)
+    ref = _gn_ref_stats(o.float(), 32, 1e-5)
+    assert (gst[..., 0] - ref[..., 0]).abs().max().item() < 1e-5 * (1 + ref[..., 0].abs().max().item())
+    assert ((gst[..., 1] - ref[..., 1]).abs() / ref[..., 1]).max().item() < 1e-4
+
+
+@pytest.mark.parametrize("M,Cc,N,geglu,residual", [(1000, 320, 960, False, True), (777, 640, 1920, False, False),
+                                                  (300, 1280, 3840, False, True), (20000, 320, 2560, True, True),
+                                                  (515, 640, 5120, True, False), (130, 1280, 10240, True, True)])
+def test_layernorm_folded_into_gemm(ops, M, Cc, N, geglu, residual):
+    """producer GEMM (x = A0 W0^T + b0 [+ res]) writes per-row (sum, sumsq) partials of x; the consumer computes
+    Linear(LayerNorm(x)) [GEGLU] with gamma folded into W, beta into the bias and mean / rstd applied in the epilogue.
+    Reference: fp32 LayerNorm + Linear on the stored bf16 x."""
+    from seva_b200 import pack
+
+    g = torch.Generator(device="cuda").manual_seed(M + N)
+    A0 = bf(torch.randn(M, 256, device="cuda", generator=g))
+    W0 = bf(torch.randn(Cc, 256, device="cuda", generator=g) / 16)
+    b0 = torch.randn(Cc, device="cuda", generator=g) * 2 + 1.0
+    res = bf(torch.randn(M, Cc, device="cuda", generator=g)) if residual else None
+    rows = torch.full((ops.ln_slots(Cc), M, 2), float("nan"), device="cuda")
+    x = ops.linear(A0, W0, b0, residual=res, ln_rowstats=rows)
+    assert torch.equal(x, ops.linear(A0, W0, b0, residual=res))
+    s_ref = x.float().sum(-1)
+    assert (rows[..., 0].sum(0) - s_ref).abs().max().item() < 2e-3 * x.float().abs().sum(-1).max().item()
+    gamma = 1 + 0.3 * torch.randn(Cc, device="cuda", generator=g)
+    beta = 0.3 * torch.randn(Cc, device="cuda", generator=g)
+    W = torch.randn(N, Cc, device="cuda", generator=g) / math.sqrt(Cc)
+    b = torch.randn(N, device="cuda", generator=g) * 0.1
+    Wg = (W * gamma[None]).to(torch.bfloat16)
+    colsum, bias2 = Wg.float().sum(1), W @ beta + b
+    if geglu:
+        bn = ops.pick_bn(N, True)
+        Wp, bp = pack.pack_geglu(Wg, bias2, bn)
+        _, cp = pack.pack_geglu(Wg, colsum, bn)
+        out = ops.linear(x, Wp, bp, geglu=True, bn=bn, ln_in=rows, ln_colsum=cp)
+    else:
+        out = ops.linear(x, Wg, bias2.contiguous(), ln_in=rows, ln_colsum=colsum.contiguous())
+    y = F.layer_norm(x.float(), (Cc,), gamma, beta, 1e-5) @ W.t() + b
+    if geglu:
+        a_, gate = y.chunk(2, dim=-1)
+        y = a_ * F.gelu(gate)
+    assert rel_l2(out, y) < 6e-3, rel_l2(out, y)
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_groupnorm_large_mean(ops, fused):
+    """groups with |mean| >> std (activations of a trained checkpoint can sit at mean / std ~ 25-100).
+    The sums are fp32; the E[x^2] - mean^2 step is done in fp64 (apply prologue / finalize)."""
+    from seva_b200 import pack
+
+    g = torch.Generator(device="cuda").manual_seed(42)
+    n_img, H, Wd, Cc = 2, 36, 36, 320
+    if fused:  # statistics from a conv epilogue whose bias puts the output at mean ~ 100, std ~ 1
+        x = bf(torch.randn(n_img, 64, H, Wd, device="cuda", generator=g))
+        w = torch.randn(Cc, 64, 3, 3, device="cuda", generator=g) / 24
+        b = torch.full((Cc,), 100.0, device="cuda") + torch.randn(Cc, device="cuda", generator=g)
+        xp = F.pad(x.permute(0, 2, 3, 1), (0, 0, 1, 1, 1, 1)).reshape(-1, 64).contiguous()
+        rpi = (H + 2) * (Wd + 2)
+        part = torch.zeros(ops.gn_partial_floats(n_img, rpi, Cc), device="cuda")
+        xin = ops.conv3x3_padded(xp, pack.pack_conv3x3(w), b, n_img, H, Wd, gn_partial=part)
+        gst = ops.groupnorm_finalize(part, Cc, rpi, n_img, H * Wd, 1e-5)
+    else:
+        xc = bf(torch.randn(n_img, H, Wd, Cc, device="cuda", generator=g) * 4.0 + 100.0)
+        xin = F.pad(xc, (0, 0, 1, 1, 1, 1)).reshape(-1, Cc).contiguous()
+        gst = None
+    gamma = torch.randn(Cc, device="cuda", generator=g)
+    beta = torch.randn(Cc, device="cuda", generator=g)
+    out = ops.groupnorm(xin, gamma, beta, n_img, H, Wd, silu=False, gstats=gst)
+    xs = xin.reshape(n_img, H + 2, Wd + 2, Cc)[:, 1:-1, 1:-1].permute(0, 3, 1, 2).float()
+    ref = F.group_norm(xs.double(), 32, gamma.double(), beta.double(), 1e-5).float()
+    got = out.reshape(n_img, H + 2, Wd + 2, Cc)[:, 1:-1, 1:-1].permute(0, 3, 1, 2)
+    assert rel_l2(got, ref) < 4e-3, rel_l2(got, ref)
+
+
+@pytest.mark.parametrize("B,heads,Lq,blocks", [(2, 5, 333, (300, 77, 411)), (1, 10, 1000, (128, 128)), (2, 2, 70, (1, 500, 64, 3))])
+def test_attention_partial_and_merge(ops, B, heads, Lq, blocks):
+    """Key blocks attended one launch at a time (the frame-shard ring): fp32 partial results + log-sum-exp, merged,
+    equal one launch over all keys."""
+    g = torch.Generator(device="cuda").manual_seed(Lq)
+    Cc = heads * 64
+    Lk = sum(blocks)
+    q = bf(torch.randn(B, Lq, Cc, device="cuda", generator=g))
+    k = bf(torch.randn(B, Lk, Cc, device="cuda", generator=g))
+    v = bf(torch.randn(B, Lk, Cc, device="cuda", generator=g))
+    full = ops.attention(q, k, v, heads)
+    parts = torch.empty(len(blocks), B, Lq, Cc, device="cuda")
+    lse = torch.empty(len(blocks), B, heads, Lq, device="cuda")
+    o = 0
+    for i, n in enumerate(blocks):
+        ops.attention_partial(q, k[:, o:o + n], v[:, o:o + n], heads, out=parts[i], lse=lse[i])
+        o += n
+    merged = ops.attention_merge(parts, lse)
+    sp = lambda t: t.reshape(B, -1, heads, 64).permute(0, 2, 1, 3).float()
+    ref = F.scaled_dot_product_attention(sp(q), sp(k), sp(v)).permute(0, 2, 1, 3).reshape(B, Lq, Cc)
+    assert rel_l2(merged, ref) < 5e-3, rel_l2(merged, ref)
+    assert rel_l2(merged, full) < 3e-3, rel_l2(merged, full)

@@ -45,12 +45,17 @@ def _net_inputs(P, B, T, h, w, seed=5):
     return x, t, y, dense
 
 
+@pytest.mark.parametrize("ring", ["ring", "off"])
 @pytest.mark.parametrize("a2a", [True, False])
 @pytest.mark.parametrize("T,B,ranks", [(5, 2, 2), (7, 1, 3), (8, 2, 4)])
-def test_frame_shard_emulated_on_one_gpu(T, B, ranks, a2a, monkeypatch):
+def test_frame_shard_emulated_on_one_gpu(T, B, ranks, a2a, ring, monkeypatch):
+    """``ring``: the 3D sites attend to one rank's K/V block per launch (seva_attn_partial) and merge -- the
+    overlapped-exchange form -- instead of one attention over gathered keys."""
     monkeypatch.setenv("SEVA_TIMEMIX_A2A", "1" if a2a else "0")
+    monkeypatch.setenv("SEVA_RING", ring)
     from seva_b200 import ops
-    from seva_b200.engine import Engine, FrameShard, _FrameGather, _SpaceExchange, pack_weights
+    from seva_b200.engine import (Engine, FrameShard, _FrameGather, _RingAttention, _RingStart, _SpaceExchange,
+                                  pack_weights)
 
     h = w = 16
     P, model = _tiny_model(T)
@@ -67,10 +72,20 @@ def test_frame_shard_emulated_on_one_gpu(T, B, ranks, a2a, monkeypatch):
         ops.pack_nchw(s.local(x.float(), B), e.net_in)
         e.bind(s.local(t, B), s.local(y, B), s.local(dense, B), ctx0=y[::T])
     stream = torch.cuda.current_stream().cuda_stream
-    n_gather = n_a2a = 0
+    n_gather = n_a2a = n_ring = 0
     for i in range(len(engs[0].calls)):
         fns = [e.calls[i][0] for e in engs]
-        if isinstance(fns[0], _SpaceExchange):   # all-to-all: rank d receives from rank r what r addressed to d
+        if isinstance(fns[0], _RingStart):       # the exchange itself: emulated at the attention entry below
+            continue
+        if isinstance(fns[0], _RingAttention):   # every rank receives every peer's [k | v] block, then attends block by block
+            n_ring += 1
+            for dst in fns:
+                for r, src in enumerate(fns):
+                    if r != dst.shard.rank:
+                        dst.peer[r].copy_(src.kvl.view(dst.peer[r].shape))
+            for dst in fns:
+                assert dst.compute(stream) == 0
+        elif isinstance(fns[0], _SpaceExchange):   # all-to-all: rank d receives from rank r what r addressed to d
             n_a2a += 1
             assert all(isinstance(f, _SpaceExchange) and f.to_space == fns[0].to_space for f in fns)
             for d, dst in enumerate(fns):
@@ -92,6 +107,9 @@ def test_frame_shard_emulated_on_one_gpu(T, B, ranks, a2a, monkeypatch):
                 fn, args = e.calls[i]
                 assert fn(*args, stream) == 0
     n3d = sum(1 for m in seva.modules() if getattr(m, "name", "") in P.unflatten_names)
+    assert n_ring == (n3d if ring == "ring" else 0)
+    if ring == "ring":
+        n3d = 0  # the 3D sites do not use the blocking gather
     if a2a:   # time-mix sites: two transposes each (the S < ranks site, if any, falls back to the K/V gather)
         assert n_a2a % 2 == 0 and n_a2a // 2 + (n_gather - n3d) == 16 and n_gather >= n3d
     else:
@@ -158,6 +176,11 @@ def _nccl_worker(rank, world, port, ret):
         model.module.set_frame_group(dist.group.WORLD)                          # plans are rebuilt
         out["frames_gather"] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()  # time-mix by K/V all-gather
         os.environ.pop("SEVA_TIMEMIX_A2A")
+        for mode in ("allgather", "off"):     # 3D sites: overlapped all-gather / blocking gather (default above: ring)
+            os.environ["SEVA_RING"] = mode
+            model.module.set_frame_group(dist.group.WORLD)
+            out["frames_" + mode] = _sample(model, inp, T, S.MultiviewCFG(1.2)).cpu()
+        os.environ.pop("SEVA_RING")
         model.module.set_frame_group(None)
         # CFG split: uncond on rank 0, cond on rank 1
         groups = D.build_groups(D.Topology(world, rank, cfg=2, sp=1))
@@ -195,11 +218,12 @@ def test_two_gpu_partitions_match_one_gpu():
             assert p.exitcode == 0, f"worker exit code {p.exitcode}"
         res = {r: dict(ret[r]) for r in range(2)}
     single = res[0]["single"]
-    # GroupNorm statistics are merged with fp32 atomics, so two runs of the same step agree to rounding, not bits
-    assert rel_l2(res[1]["single"], single) < 1e-2, rel_l2(res[1]["single"], single)
+    assert torch.equal(res[1]["single"], single)   # no atomics anywhere on the path: two GPUs, the same bits
     for r in range(2):
         assert rel_l2(res[r]["frames"], single) < 2e-2, rel_l2(res[r]["frames"], single)
         assert rel_l2(res[r]["frames_gather"], single) < 2e-2, rel_l2(res[r]["frames_gather"], single)
+        assert rel_l2(res[r]["frames_allgather"], single) < 2e-2 and rel_l2(res[r]["frames_off"], single) < 2e-2
+        assert rel_l2(res[r]["frames_allgather"], res[r]["frames_gather"]) < 1e-6   # same blocks, same merge order
         assert rel_l2(res[r]["cfg"], single) < 2e-2, rel_l2(res[r]["cfg"], single)
     # the gathered tensors are the same bits on every rank, so the replicated sampler state cannot drift apart
     assert torch.equal(res[0]["frames"], res[1]["frames"]) and torch.equal(res[0]["cfg"], res[1]["cfg"])

@@ -89,3 +89,52 @@ def test_two_pass_scene_matches_oracle_schedule():
     assert ours.shape == ref.shape == (n_targets, 4, h, h)
     err = ((ours - ref).norm() / ref.norm()).item()
     assert err < 5e-2, err  # final latents after two chained bf16 passes vs fp32 (north_star: <= 5e-2)
+
+
+def test_window_latents_do_not_depend_on_who_samples_them():
+    """with the REAL sampler (per-step ``randn_like`` noise) a window must give the same latents whether it
+    is sampled after the other windows on one rank or alone on another rank.  The scene seeds every window's noise
+    stream from (scene seed, pass, window): sampling the second pass's windows in REVERSE order on a polluted RNG
+    reproduces the sequential run bit for bit."""
+    T, h, steps, n_targets = 4, 16, 2, 9
+    prm = SevaParams(model_channels=64, num_frames=T)
+    with torch.device("meta"):
+        m = Seva(prm)
+    sd = synth.fill_state_dict({k: tuple(v.shape) for k, v in m.state_dict().items()}, seed=0)
+    m.load_state_dict(sd, assign=True)
+    model = SGMWrapper(m.eval()).to("cuda")
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device="cuda")
+    make_sampler = lambda T_, wrap: S.EulerEDMSampler(disc, S.MultiviewCFG(1.2), num_steps=steps, s_churn=0.0, s_tmin=0.0,
+                                                      s_tmax=999.0, s_noise=1.0, verbose=False, device="cuda")
+    g = torch.Generator().manual_seed(5)
+    traj, inp = PC.cameras(n_targets, 3), PC.cameras(1, 4)
+    opts = {"chunk_strategy": "interp", "chunk_strategy_first_pass": "gt-nearest", "cfg": 2.0}
+    version = {"T": [T, T], "options": opts}
+    prior = P.infer_prior_inds(traj, P.infer_prior_stats([T, T], 1, n_targets, version), [], opts)
+    sc = SC.Scene(torch.randn(1, 4, h, h, generator=g), inp, _K(1), traj, _K(n_targets), [0],
+                  list(range(1, n_targets + 1)), traj[prior], _K(len(prior)), [int(i) + 1 for i in prior])
+    plan = SC.plan_scene(sc, version["T"], opts, task="img2trajvid", use_traj_prior=True)
+    codec = SC.Codec(dim=prm.context_dim)
+    seen = {}
+
+    def recording(model_, den_, sampler_, win, rows, all_c2ws, x0, cfg, codec_, camera_scale, device):
+        out = SC.sample_window(model_, den_, sampler_, win, rows, all_c2ws, x0, cfg, codec_, camera_scale, device)
+        seen.setdefault("calls", []).append((win, rows, all_c2ws, x0, cfg, out))
+        return out
+
+    a = SC.run_scene(sc, plan, model, denoiser, make_sampler, codec=codec, generator=torch.Generator().manual_seed(7),
+                     sample_fn=recording)
+    b = SC.run_scene(sc, plan, model, denoiser, make_sampler, codec=codec, generator=torch.Generator().manual_seed(7))
+    assert torch.equal(a, b)
+    n_first = len(plan.passes[0].windows)
+    second = seen["calls"][n_first:]
+    assert len(second) >= 2
+    sampler = make_sampler(T, None)
+    torch.cuda.manual_seed(999)
+    torch.randn(1000, device="cuda")  # another rank's RNG history
+    for k in reversed(range(len(second))):
+        win, rows, all_c2ws, x0, cfg, want = second[k]
+        SC._seed_step_noise("cuda", SC.window_noise_seed(7, 1, k))
+        got = SC.sample_window(model, denoiser, sampler, win, rows, all_c2ws, x0, cfg, codec, 2.0, "cuda")
+        assert torch.equal(got, want), k

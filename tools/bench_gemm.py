@@ -16,6 +16,8 @@ flush = torch.empty(256 * 1024 * 1024, device=dev, dtype=torch.uint8)
 filt = sys.argv[1] if len(sys.argv) > 1 else ""
 CL = int(os.environ.get("SEVA_CLUSTER", "0"))
 BN = int(os.environ.get("SEVA_BN", "0"))
+LNF = int(os.environ.get("SEVA_LNFOLD", "0"))   # 1: the geglu / no-residual linear cases fold a LayerNorm of A (row statistics given)
+LNR = int(os.environ.get("SEVA_LNROWS", "0"))   # 1: the residual linear cases also write LayerNorm row statistics of their output
 
 
 def timeit(fn, n=5):
@@ -53,18 +55,29 @@ for kind, M, N, K, has_res in LIN:
     A = rnd(M, K).bfloat16()
     W = (rnd(N, K) / math.sqrt(K)).bfloat16()
     b = rnd(N) * 0.1
+    ln_kw = {}
+    if LNF and (kind == "geglu" or not has_res):
+        # row statistics of A as its producer would have left them (K columns, split over the producer's slots)
+        slots = ops.ln_slots(K)
+        Af = A.float()
+        st = torch.stack([Af.sum(1), (Af * Af).sum(1)], -1) / slots
+        ln_kw = dict(ln_in=st[None].repeat(slots, 1, 1).contiguous(), ln_colsum=W.float().sum(1).contiguous())
     if kind == "geglu":
         bn = ops.pick_bn(N, True)
         Wp, bp = pack.pack_geglu(W, b, bn)
+        if ln_kw:
+            ln_kw["ln_colsum"] = pack.pack_geglu(W, W.float().sum(1), bn)[1]
         out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
-        fn = lambda: ops.linear(A, Wp, bp, geglu=True, out=out, cluster=CL)
+        fn = lambda: ops.linear(A, Wp, bp, geglu=True, out=out, cluster=CL, **ln_kw)
     else:
         res = rnd(M, N).bfloat16() if has_res else None
         out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-        fn = lambda: ops.linear(A, W, b, out=out, residual=res, cluster=CL, bn=BN)
+        rows_kw = dict(ln_rowstats=torch.empty(ops.ln_slots(N, BN), M, 2, device=dev)) if LNR and N in (320, 640, 1280) else {}
+        fn = lambda: ops.linear(A, W, b, out=out, residual=res, cluster=CL, bn=BN, **ln_kw, **rows_kw)
     t = timeit(fn)
     def ref(rows):
-        y = A[rows].float() @ W.float().t() + b
+        Ar = F.layer_norm(A[rows].float(), (K,), None, None, 1e-5) if ln_kw else A[rows].float()
+        y = Ar @ W.float().t() + b
         if kind == "geglu":
             x_, g_ = y.chunk(2, -1)
             return x_ * F.gelu(g_)
