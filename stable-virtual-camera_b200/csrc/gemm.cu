@@ -76,9 +76,11 @@ struct GemmArgs {
 
 // ---- GEGLU: x * gelu(g), exact (erf) GELU --------------------------------------------------------------
 // g * Phi(g) is evaluated as g * sigmoid(2 g p(g^2)) with p = c0 + c1 g^2 + c2 g^4 fitted to the erf form
-// (minimax over the real line, g^2 clamped at the vertex of p): max |error| 2.8e-5, i.e. 40x below the bf16
-// rounding of the stored product.  Two MUFU ops (ex2, rcp) and 4.5 packed-fp32 issue slots per element,
-// against 15 + 2 for a 7.1.26 erf -- the K = 320 GEGLU GEMMs are epilogue-bound otherwise.
+// (minimax over the real line, g^2 clamped at the vertex of p): max |error| of the fit 2.8e-5.  The sigmoid is
+// 0.5 + 0.5 tanh(g p): ONE MUFU op (tanh.approx, |error| <= 2^-11 on tanh, so <= 2.4e-4 on Phi -- below the bf16
+// rounding of the stored product wherever the product is not itself negligible) and 4 packed-fp32 issue slots per
+// element, against 15 + 2 for a 7.1.26 erf: the K = 320 GEGLU GEMMs are epilogue-bound (r2d: 424 -> 393 us against the
+// ex2 + rcp form, which -DSEVA_GEGLU_EX2 restores; full-model parity unchanged at 3.07e-3).
 __device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
   return (unsigned long long)__float_as_uint(lo) | ((unsigned long long)__float_as_uint(hi) << 32);
 }
@@ -103,22 +105,22 @@ __device__ __forceinline__ float hi2(unsigned long long v) { return __uint_as_fl
 
 // (x0, x1) <- (x0 * gelu(g0), x1 * gelu(g1))
 __device__ __forceinline__ void geglu2(float& x0, float& x1, float g0, float g1) {
+#ifndef SEVA_GEGLU_EX2
+  constexpr float kC0 = 0.7974855517f, kC1 = 0.0370259212f, kC2 = -0.000354804609f;  // sigmoid(2 g p(g^2)) ~ Phi(g)
+#else
   constexpr float kC0 = -2.3010568618774414f;    // -2 log2(e) * 0.7974855517
   constexpr float kC1 = -0.10683422535657883f;   // -2 log2(e) * 0.0370259212
   constexpr float kC2 = 0.0010237497044727206f;  // -2 log2(e) * -0.000354804609
+#endif
   const unsigned long long g = pk2(g0, g1);
   const unsigned long long gg = mul2(g, g);
   const unsigned long long g2 = pk2(fminf(lo2(gg), 52.0f), fminf(hi2(gg), 52.0f));
   unsigned long long p = fma2(pk2(kC2, kC2), g2, pk2(kC1, kC1));
   p = fma2(p, g2, pk2(kC0, kC0));
   const unsigned long long u = mul2(g, p);
-#ifdef SEVA_GEGLU_TANH
-  // sigmoid(2 y) = 0.5 + 0.5 tanh(y), y = g p(g^2) = u / (-2 log2 e): ONE MUFU op per element instead of two
-  // (tanh.approx: |error| <= 2^-11, i.e. up to 2.4e-4 on Phi -- measurably noisier than the ex2 + rcp form on strongly
-  // negative gates, which is why this is an A/B build and not the default)
-  constexpr float kS = -0.34657359027997264f;  // -ln(2) / 2
-  const unsigned long long y = mul2(u, pk2(kS, kS));
-  const unsigned long long h = fma2(pk2(fast_tanh(lo2(y)), fast_tanh(hi2(y))), pk2(0.5f, 0.5f), pk2(0.5f, 0.5f));
+#ifndef SEVA_GEGLU_EX2
+  // sigmoid(2 u) = 0.5 + 0.5 tanh(u)
+  const unsigned long long h = fma2(pk2(fast_tanh(lo2(u)), fast_tanh(hi2(u))), pk2(0.5f, 0.5f), pk2(0.5f, 0.5f));
   const unsigned long long o = mul2(mul2(pk2(x0, x1), g), h);
 #else
   const unsigned long long e1p = add2(pk2(fast_exp2(lo2(u)), fast_exp2(hi2(u))), pk2(1.0f, 1.0f));  // 1 + exp(-2 g p)
@@ -242,6 +244,7 @@ __device__ __forceinline__ void col_stats(const EpiStats& st, int lane, const in
 // tinfo[i] describes tile row 8*i + lane/4 of this warp's 32 rows: -1 = skip, else out_row | border << 30.
 // Lane (r, p = lane & 3) of the transposed view owns columns [8p, 8p+8) of the 32-column chunk.
 // No residual: pack to bf16 in the row-per-thread view, transpose 32 rows x 64 B, store.
+template <bool kStats>
 __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t patch, int lane,
                                                  const int (&tinfo)[4], const float (&f)[32], int border,
                                                  int n, const EpiStats& st) {
@@ -273,7 +276,7 @@ __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t pat
   for (int i = 0; i < 4; ++i)
     if (tinfo[i] >= 0)
       *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u[i];
-  if (st.gn_part != nullptr) {  // statistics of the values as stored (bf16-rounded)
+  if (kStats && st.gn_part != nullptr) {  // statistics of the values as stored (bf16-rounded)
     float v[4][8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -287,6 +290,7 @@ __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t pat
 
 // Residual: transpose the fp32 values (32 rows x 128 B), add the bf16 residual read with the same
 // coalesced mapping (already in registers: issued before the TMEM load), round once, store.
+template <bool kStats>
 __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patch, int lane,
                                                 const int (&tinfo)[4], const float (&f)[32],
                                                 const uint4 (&res)[4], int n, EpiStats& st) {
@@ -329,13 +333,13 @@ __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patc
         u.w = pack_bf16x2(v[i][6], v[i][7]);
       }
       *reinterpret_cast<uint4*>(obase + (long long)(tinfo[i] & 0x3fffffff) * a.ldo) = u;
-      if (st.rows_on || st.gn_part != nullptr) {  // statistics of the values as stored (bf16-rounded)
+      if (kStats && (st.rows_on || st.gn_part != nullptr)) {  // statistics of the values as stored (bf16-rounded)
         v[i][0] = bf16_lo(u.x); v[i][1] = bf16_hi(u.x); v[i][2] = bf16_lo(u.y); v[i][3] = bf16_hi(u.y);
         v[i][4] = bf16_lo(u.z); v[i][5] = bf16_hi(u.z); v[i][6] = bf16_lo(u.w); v[i][7] = bf16_hi(u.w);
       }
     }
   }
-  if (st.rows_on) {
+  if (kStats && st.rows_on) {
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -344,11 +348,13 @@ __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patc
         st.rq[i] = fmaf(v[i][j], v[i][j], st.rq[i]);
       }
   }
-  if (st.gn_part != nullptr) col_stats(st, lane, tinfo, v, n);
+  if (kStats && st.gn_part != nullptr) col_stats(st, lane, tinfo, v, n);
   __syncwarp();
 }
 
-template <int kCtas>
+// kStats: the output-statistics / LayerNorm-fold epilogue paths are compiled in.  Plain launches take the kStats = false
+// instantiation, whose epilogue carries none of their registers (ptxas: 168 registers + spills with, see the Makefile log).
+template <int kCtas, bool kStats>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const GemmArgs a) {
@@ -551,7 +557,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       return r;
     };
-    const bool ln_fold = a.fast && a.ln_in != nullptr;
+    const bool ln_fold = kStats && a.fast && a.ln_in != nullptr;
     auto fetch_cs = [&](int tile_) -> float4 {  // LayerNorm column sums, same lane -> column map as fetch_cb
       float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
       if (!ln_fold || tile_ >= a.num_tiles) return r;
@@ -609,11 +615,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     float4 cs_next = fetch_cs(cluster_id);
     fetch_ln(cluster_id);
     EpiStats st;
-    st.gn_part = a.fast ? a.gn_part : nullptr;
+    st.gn_part = kStats && a.fast ? a.gn_part : nullptr;
     st.gn_ld = a.Nout;
     st.gn_slots = a.gn_slots;
     st.gn_rpi = a.gn_rpi;
-    st.rows_on = a.fast && a.ln_rows != nullptr && a.residual != nullptr;
+    st.rows_on = kStats && a.fast && a.ln_rows != nullptr && a.residual != nullptr;
+    float2* const ln_rows = kStats && a.fast ? a.ln_rows : nullptr;
     uint32_t tl = 0;
     for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
       const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
@@ -683,7 +690,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
         for (int i = 0; i < 4; ++i) tinfo[i] = __shfl_sync(0xffffffffu, info, 8 * i + (lane >> 2));
       }
-      if (st.gn_part != nullptr) {
+      if (kStats && st.gn_part != nullptr) {
         const int img = ri.valid ? m / a.gn_rpi : -1;
 #pragma unroll
         for (int i = 0; i < 4; ++i) st.timg[i] = __shfl_sync(0xffffffffu, img, 8 * i + (lane >> 2));
@@ -708,8 +715,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (u_begin >= u_end) {
         mbar_wait(bar_tfull + 8 * as, aph);
         release_tmem();
-        if (a.fast && a.ln_rows != nullptr && ri.valid)  // a part without columns still owns its slot
-          a.ln_rows[(long long)(tile_n * kParts + part) * a.M + m] = make_float2(0.f, 0.f);
+        if (ln_rows != nullptr && ri.valid)  // a part without columns still owns its slot
+          ln_rows[(long long)(tile_n * kParts + part) * a.M + m] = make_float2(0.f, 0.f);
       } else if (!a.geglu) {
         for (int c = u_begin; c < u_end; ++c) {
           const int n = n0 + c * 32;
@@ -748,9 +755,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               for (int j = 0; j < 32; ++j) f[j] += __ldg(r1 + j) - __ldg(r0 + j);
             }
             if (a.residual != nullptr) {
-              store_chunk_res(a, patch, lane, tinfo, f, res, n, st);
+              store_chunk_res<kStats>(a, patch, lane, tinfo, f, res, n, st);
             } else {
-              if (a.ln_rows != nullptr) {
+              if (ln_rows != nullptr) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                   const float r = __bfloat162float(__float2bfloat16(f[j]));  // the value as stored
@@ -758,7 +765,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                   row_q = fmaf(r, r, row_q);
                 }
               }
-              store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n, st);
+              store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n, st);
             }
           } else {
             if (a.bias != nullptr) {
@@ -769,8 +776,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             finish_store32(a, ri, f, n);
           }
         }
-        if (a.fast && a.ln_rows != nullptr) {
-          float2* dst = a.ln_rows + (long long)(tile_n * kParts + part) * a.M;
+        if (ln_rows != nullptr) {
+          float2* dst = ln_rows + (long long)(tile_n * kParts + part) * a.M;
           if (a.residual != nullptr) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -819,10 +826,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               g[j] += __ldg(a.bias + ng + j);
             }
           }
+          if (!SEVA_DBG(a, 8)) {   // (debug builds: bit 8 skips the activation, bit 16 the store)
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) geglu2(f[j], f[j + 1], g[j], g[j + 1]);
+            for (int j = 0; j < 32; j += 2) geglu2(f[j], f[j + 1], g[j], g[j + 1]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] += g[j];
+          }
           const int n_out = tile_n * (a.bn / 2) + p * 32;
-          if (a.fast) store_chunk_bf16(a, patch, lane, tinfo, f, ri.border, n_out, st);
+          if (SEVA_DBG(a, 16)) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc += f[j];
+            if (acc == 1.2345e30f) reinterpret_cast<float*>(a.out)[0] = acc;  // keeps the values live
+            continue;
+          }
+          if (a.fast) store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n_out, st);
           else finish_store32(a, ri, f, n_out);
         }
       }
@@ -1023,14 +1042,18 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   }
 
   const int smem = a.wstat ? fixed + wstat_bytes + stages * (BM * BK * 2) : fixed + stages * stage_bytes;
-  if (ensure_dyn_smem(ctas == 1 ? reinterpret_cast<const void*>(gemm_kernel<1>) : reinterpret_cast<const void*>(gemm_kernel<2>),
-                      kSmemMax))
-    return 2;
+  const bool stats = a.gn_part != nullptr || a.ln_rows != nullptr || a.ln_in != nullptr;
+  const void* kfn = ctas == 1 ? (stats ? reinterpret_cast<const void*>(gemm_kernel<1, true>)
+                                       : reinterpret_cast<const void*>(gemm_kernel<1, false>))
+                              : (stats ? reinterpret_cast<const void*>(gemm_kernel<2, true>)
+                                       : reinterpret_cast<const void*>(gemm_kernel<2, false>));
+  if (ensure_dyn_smem(kfn, kSmemMax)) return 2;
   if (ctas == 1) {
     int grid = sms;
     if (grid > a.num_tiles) grid = a.num_tiles;
     if (a.wstat) grid = wstat_grid;
-    gemm_kernel<1><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
+    if (stats) gemm_kernel<1, true><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
+    else gemm_kernel<1, false><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
   } else {
     int pairs = sms / 2;
     if (pairs > a.num_tiles) pairs = a.num_tiles;
@@ -1047,7 +1070,8 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2>, tmA, tmB, a));
+    if (stats) SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, true>, tmA, tmB, a));
+    else SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, false>, tmA, tmB, a));
   }
   SEVA_CUDA(cudaGetLastError());
   return 0;
