@@ -218,6 +218,14 @@ int seva_upsample2x_pad(const void* src, int64_t lds, void* dst, int64_t ldd, in
  * dst compact [N*(h/2)*(w/2), 9*C] with column tap*C + c. */
 int seva_im2col3x3_s2(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
                       int32_t C, void* stream);
+/* Same gather with the window origin moved by `origin` (0 or 1) padded rows / columns: origin 1 is the VAE's
+ * Downsample2D (diffusers: F.pad(x, (0, 1, 0, 1)) + 3x3 stride-2 conv, padding 0; seva/modules/autoencoder.py:13 loads it). */
+int seva_im2col3x3_s2_at(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
+                         int32_t C, int32_t origin, void* stream);
+/* Row softmax of fp32 scores x [rows, L] (row stride ldx) into bf16 probabilities y (row stride ldy): the softmax of the
+ * VAE mid-block attention (diffusers Attention / AttnProcessor2_0, one head of width 512), whose scores come from
+ * seva_gemm_bf16 with out_fp32. */
+int seva_softmax_rows(const float* x, int64_t ldx, void* y, int64_t ldy, int32_t rows, int32_t L, void* stream);
 /* fp32 rows -> bf16 rows (used for packing small inputs). */
 int seva_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 

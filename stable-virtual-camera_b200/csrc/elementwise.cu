@@ -388,10 +388,12 @@ upsample2x_pad_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv
   *reinterpret_cast<uint4*>(dst + drow * ldd + cv * 8) = v;
 }
 
-// 3x3 stride-2 pad-1 gather: dst[(n, yo, xo), tap*C + c] = src_padded[n, 2*yo + dy, 2*xo + dx, c]
+// 3x3 stride-2 gather: dst[(n, yo, xo), tap*C + c] = src_padded[n, 2*yo + dy + origin, 2*xo + dx + origin, c]
+// origin 0: symmetric pad 1 (Seva's Downsample, layers.py:54-58); origin 1: pad right/bottom only (the VAE's
+// Downsample2D: F.pad(x, (0, 1, 0, 1)) then a stride-2 conv without padding)
 __global__ void __launch_bounds__(256)
 im2col3x3_s2_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv_bfloat16* __restrict__ dst,
-                    int N, int h, int w, int C) {
+                    int N, int h, int w, int C, int origin) {
   const int CV = C >> 3;
   const int ho = h >> 1, wo = w >> 1;
   const long long total = (long long)N * ho * wo * 9 * CV;
@@ -406,7 +408,7 @@ im2col3x3_s2_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv_b
   const int yo = (int)(r % ho);
   const int n = (int)(r / ho);
   // output (yo, xo) reads input rows 2*yo-1+dy = padded rows 2*yo + dy
-  const int yp = 2 * yo + tap / 3, xp = 2 * xo + tap % 3;
+  const int yp = 2 * yo + tap / 3 + origin, xp = 2 * xo + tap % 3 + origin;
   const long long srow = (long long)n * (h + 2) * (w + 2) + (long long)yp * (w + 2) + xp;
   const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + srow * lds + cv * 8));
   const long long drow = ((long long)n * ho + yo) * wo + xo;
@@ -688,18 +690,24 @@ extern "C" int seva_upsample2x_pad(const void* src, int64_t lds, void* dst, int6
   return 0;
 }
 
-extern "C" int seva_im2col3x3_s2(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
-                                 int32_t C, void* stream_v) {
+extern "C" int seva_im2col3x3_s2_at(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
+                                    int32_t C, int32_t origin, void* stream_v) {
   if (check_device()) return 3;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
   SEVA_CHECK(src && dst, "seva_im2col3x3_s2: null pointer");
   SEVA_CHECK((C % 8) == 0 && (lds % 8) == 0 && (h % 2) == 0 && (w % 2) == 0,
              "seva_im2col3x3_s2: need C %% 8 == 0 and even h, w");
+  SEVA_CHECK(origin == 0 || origin == 1, "seva_im2col3x3_s2: origin must be 0 or 1");
   const long long total = (long long)N * (h / 2) * (w / 2) * 9 * (C / 8);
   im2col3x3_s2_kernel<<<blocks_for(total, 256), 256, 0, stream>>>(
-      reinterpret_cast<const __nv_bfloat16*>(src), lds, reinterpret_cast<__nv_bfloat16*>(dst), N, h, w, C);
+      reinterpret_cast<const __nv_bfloat16*>(src), lds, reinterpret_cast<__nv_bfloat16*>(dst), N, h, w, C, origin);
   SEVA_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int seva_im2col3x3_s2(const void* src, int64_t lds, void* dst, int32_t N, int32_t h, int32_t w,
+                                 int32_t C, void* stream_v) {
+  return seva_im2col3x3_s2_at(src, lds, dst, N, h, w, C, 0, stream_v);
 }
 
 extern "C" int seva_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream_v) {

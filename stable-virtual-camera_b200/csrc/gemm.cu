@@ -63,6 +63,7 @@ struct GemmArgs {
   int reverse;  // 1: walk the tile list backwards (L2-aware traversal, see seva_b200.h)
   int fast;  // 1: bf16 output, N % 32 == 0 and 16-byte aligned pointers/strides -> coalesced epilogue
   int wstat;  // 1: weight-stationary walk (opt-in): the CTA's N tile of W stays in smem for all of its M tiles
+  int tma_store;  // 1: plain row-mapped bf16 output without residual: 32 x 32 boxes leave through TMA stores
   // ---- statistics of the OUTPUT, for the normalisation that consumes it (coalesced bf16 epilogue only) ----
   float* gn_part;      // GroupNorm: [image][slot][N][2] partial (sum, sum of squares) per 32-row block, or null
   int gn_rpi, gn_slots;
@@ -288,6 +289,34 @@ __device__ __forceinline__ void store_chunk_bf16(const GemmArgs& a, uint32_t pat
   __syncwarp();
 }
 
+// Same packing, but the 32 rows x 64 B box leaves through ONE TMA store issued by lane 0 (the patch layout above IS the
+// 64-byte TMA swizzle: 16-byte chunk index ^ address bits 7..8): no transposed read-back, no per-row address arithmetic,
+// no STG -- r2f measured the store half of the K = 320 GEGLU epilogue at 62 of 347 us.  Rows past M are clipped by the
+// tensor map.  `buf` alternates between the two 2 KB halves of the warp's patch; lane 0 first waits until the store issued
+// two chunks ago has finished READING its half.
+__device__ __forceinline__ void store_chunk_tma(const CUtensorMap* tmO, uint32_t buf, int lane, const float (&f)[32],
+                                                int border, int n, int mrow0) {
+  if (lane == 0) tma_store_wait_read<1>();
+  __syncwarp();
+  const uint32_t row = buf + lane * 64;
+  const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint32_t w0 = pack_bf16x2(f[8 * q + 0], f[8 * q + 1]);
+    uint32_t w1 = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+    uint32_t w2 = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]);
+    uint32_t w3 = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+    if (border) w0 = w1 = w2 = w3 = 0u;
+    sts128(row + ((q ^ sw) << 4), w0, w1, w2, w3);
+  }
+  fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_2d(tmO, buf, n, mrow0);
+    tma_store_commit();
+  }
+}
+
 // Residual: transpose the fp32 values (32 rows x 128 B), add the bf16 residual read with the same
 // coalesced mapping (already in registers: issued before the TMEM load), round once, store.
 template <bool kStats>
@@ -357,7 +386,7 @@ __device__ __forceinline__ void store_chunk_res(const GemmArgs& a, uint32_t patc
 template <int kCtas, bool kStats>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const GemmArgs a) {
+            const __grid_constant__ CUtensorMap tmO, const GemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   // control block
@@ -389,6 +418,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (a.tma_store) tma_prefetch_desc(&tmO);
     for (int s = 0; s < a.stages; ++s) {
       mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, 1);
@@ -621,7 +651,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     st.gn_rpi = a.gn_rpi;
     st.rows_on = kStats && a.fast && a.ln_rows != nullptr && a.residual != nullptr;
     float2* const ln_rows = kStats && a.fast ? a.ln_rows : nullptr;
-    uint32_t tl = 0;
+    const bool tma_out = !kStats && a.tma_store;
+    uint32_t tl = 0, sc = 0;  // sc: chunks stored so far (TMA path: which half of the patch is next)
     for (int tile = cluster_id; tile < a.num_tiles; tile += n_clusters, ++tl) {
       const uint32_t as = tl & 1, aph = (tl >> 1) & 1;
       const int pt = a.reverse ? a.num_tiles - 1 - tile : tile;
@@ -765,7 +796,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                   row_q = fmaf(r, r, row_q);
                 }
               }
-              store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n, st);
+              if (tma_out) store_chunk_tma(&tmO, patch + ((sc++ & 1u) << 11), lane, f, ri.border, n, m0 + quarter * 32);
+              else store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n, st);
             }
           } else {
             if (a.bias != nullptr) {
@@ -841,11 +873,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (acc == 1.2345e30f) reinterpret_cast<float*>(a.out)[0] = acc;  // keeps the values live
             continue;
           }
-          if (a.fast) store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n_out, st);
+          if (tma_out) store_chunk_tma(&tmO, patch + ((sc++ & 1u) << 11), lane, f, ri.border, n_out, m0 + quarter * 32);
+          else if (a.fast) store_chunk_bf16<kStats>(a, patch, lane, tinfo, f, ri.border, n_out, st);
           else finish_store32(a, ri, f, n_out);
         }
       }
     }
+    if (tma_out && lane == 0) tma_store_wait<0>();  // the patch must outlive the last stores' reads
   }
 
   tc_fence_before();
@@ -870,6 +904,25 @@ static int pick_bn(int N, int geglu) {
       best = bn;
       best_pad = pad;
     }
+  }
+  return best;
+}
+
+// Long-K problems with few tiles per CTA: the default N tile (least padding, widest) can leave the last wave mostly
+// empty -- the 9 x 9 convs are 20 x 5 tiles of 256 x 256 on 74 CTA pairs = 2 waves for 1.35 waves of work.  Model a
+// launch as waves x (bn + 96) (tile time: MMA ~ bn plus a per-tile cost; fitted to r2f: bn 256 / 192 / 160 / 128 =
+// 125 / 102 / 131 / 129 us at 42 x 9 x 9 x 1280 -> 1280, 309 / - / 344 / 369 us at 18 x 18) and take a narrower tile only
+// when the model promises at least 8 %.
+static int pick_bn_waves(int N, int m_tiles, int units, int bn0) {
+  auto cost = [&](int bn) {
+    const long long tiles = (long long)m_tiles * ((N + bn - 1) / bn);
+    return ((tiles + units - 1) / units) * (long long)(bn + 96);
+  };
+  int best = bn0;
+  long long best_cost = cost(bn0);
+  for (int bn = 256; bn >= 128; bn -= 32) {
+    const long long c = cost(bn);
+    if (c * 100 < best_cost * 92 && c < cost(best)) best = bn;
   }
   return best;
 }
@@ -903,6 +956,9 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
              "seva_gemm_bf16: A/W must be 16-byte aligned");
   SEVA_CHECK(!g->geglu || (g->N % 2) == 0, "seva_gemm_bf16: GEGLU needs even N");
   int bn = g->bn > 0 ? g->bn : pick_bn(g->N, g->geglu);
+  if (g->bn <= 0 && !g->geglu && g->cluster != 1 && (long long)g->ntaps * g->Kc >= 1024 && g->M > BM &&
+      g->ln_rowstats == nullptr && g->ln_in_stats == nullptr && (g->N % 32) == 0)
+    bn = pick_bn_waves(g->N, (g->M + 2 * BM - 1) / (2 * BM), sm_count() / 2, bn);   // these launches run as CTA pairs
   SEVA_CHECK(bn % 32 == 0 && bn <= 256 && bn >= 32 && (!g->geglu || bn % 64 == 0),
              "seva_gemm_bf16: bad N tile %d", bn);
   SEVA_CHECK(!g->geglu || (g->N % bn) == 0, "seva_gemm_bf16: GEGLU needs N %% bn == 0");
@@ -1043,6 +1099,14 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
 
   const int smem = a.wstat ? fixed + wstat_bytes + stages * (BM * BK * 2) : fixed + stages * stage_bytes;
   const bool stats = a.gn_part != nullptr || a.ln_rows != nullptr || a.ln_in != nullptr;
+  CUtensorMap tmO = tmA;  // placeholder when the TMA-store epilogue is off (never dereferenced)
+  a.tma_store = a.fast && !stats && g->out_map == 0 && g->residual == nullptr;
+  if (a.tma_store) {
+    const uint64_t dims[2] = {(uint64_t)a.Nout, (uint64_t)g->M};
+    const uint64_t strides[1] = {(uint64_t)g->ldo * 2};
+    const uint32_t box[2] = {32, 32};
+    if (make_tmap_bf16_sw(&tmO, g->out, 2, dims, strides, box, 64)) return 4;
+  }
   const void* kfn = ctas == 1 ? (stats ? reinterpret_cast<const void*>(gemm_kernel<1, true>)
                                        : reinterpret_cast<const void*>(gemm_kernel<1, false>))
                               : (stats ? reinterpret_cast<const void*>(gemm_kernel<2, true>)
@@ -1052,8 +1116,8 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
     int grid = sms;
     if (grid > a.num_tiles) grid = a.num_tiles;
     if (a.wstat) grid = wstat_grid;
-    if (stats) gemm_kernel<1, true><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
-    else gemm_kernel<1, false><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, a);
+    if (stats) gemm_kernel<1, true><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmO, a);
+    else gemm_kernel<1, false><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmO, a);
   } else {
     int pairs = sms / 2;
     if (pairs > a.num_tiles) pairs = a.num_tiles;
@@ -1070,8 +1134,8 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (stats) SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, true>, tmA, tmB, a));
-    else SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, false>, tmA, tmB, a));
+    if (stats) SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, true>, tmA, tmB, tmO, a));
+    else SEVA_CUDA(cudaLaunchKernelEx(&cfg, gemm_kernel<2, false>, tmA, tmB, tmO, a));
   }
   SEVA_CUDA(cudaGetLastError());
   return 0;

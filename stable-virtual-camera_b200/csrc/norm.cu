@@ -884,6 +884,62 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Row softmax, fp32 scores -> bf16 probabilities: the VAE mid-block attention (one head of width 512 over h*w tokens;
+// diffusers Attention with upcast softmax) runs as S = q k^T (GEMM, fp32) -> this -> P v (GEMM).  One block per row,
+// two passes over the row (max, then exp / sum with the exponentials parked in shared memory when the row fits).
+// ------------------------------------------------------------------------------------------------
+constexpr int kSoftmaxSmemFloats = 12224;  // just under 48 KB of static shared memory: rows up to 12224 keep their exponentials on chip
+
+__global__ void __launch_bounds__(256)
+softmax_rows_kernel(const float* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y, long long ldy, int L) {
+  __shared__ float ex[kSoftmaxSmemFloats];
+  __shared__ float red[8];
+  const float* xr = x + (long long)blockIdx.x * ldx;
+  __nv_bfloat16* yr = y + (long long)blockIdx.x * ldy;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float m = -INFINITY;
+  for (int i = tid; i < L; i += 256) m = fmaxf(m, __ldg(xr + i));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (lane == 0) red[warp] = m;
+  __syncthreads();
+  m = red[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) m = fmaxf(m, red[w]);
+  __syncthreads();
+  const bool cached = L <= kSoftmaxSmemFloats;
+  float sum = 0.0f;
+  for (int i = tid; i < L; i += 256) {
+    const float e = __expf(__ldg(xr + i) - m);
+    if (cached) ex[i] = e;
+    sum += e;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) red[warp] = sum;
+  __syncthreads();
+  sum = 0.0f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) sum += red[w];   // same order in every thread: one value per row
+  const float inv = 1.0f / sum;
+  for (int i = tid; i < L; i += 256) {
+    const float e = cached ? ex[i] : __expf(__ldg(xr + i) - m);
+    yr[i] = __float2bfloat16(e * inv);
+  }
+}
+
+extern "C" int seva_softmax_rows(const float* x, int64_t ldx, void* y, int64_t ldy, int32_t rows, int32_t L,
+                                 void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(x && y && rows > 0 && L > 0 && ldx >= L && ldy >= L, "seva_softmax_rows: bad arguments");
+  softmax_rows_kernel<<<rows, 256, 0, stream>>>(x, ldx, reinterpret_cast<__nv_bfloat16*>(y), ldy, L);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int seva_layernorm(const void* x, int64_t ldx, void* y, int64_t ldy, const float* gamma,
                               const float* beta, int32_t M, int32_t C, float eps, int32_t reverse, void* stream_v) {
   using namespace seva;

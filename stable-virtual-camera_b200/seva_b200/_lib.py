@@ -81,6 +81,8 @@ _PROTOS = {
     "seva_unpack_nchw": [c_void_p, c_i64, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "seva_upsample2x_pad": [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_int, c_void_p],
     "seva_im2col3x3_s2": [c_void_p, c_i64, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
+    "seva_im2col3x3_s2_at": [c_void_p, c_i64, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "seva_softmax_rows": [c_void_p, c_i64, c_void_p, c_i64, c_int, c_int, c_void_p],
     "seva_cast_f32_bf16": [c_void_p, c_void_p, c_i64, c_void_p],
     "seva_timestep_embedding": [c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
     "seva_gemv_grouped": [c_void_p, c_int, c_int, c_int, c_int, c_void_p],

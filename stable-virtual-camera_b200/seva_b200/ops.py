@@ -453,9 +453,21 @@ def upsample2x_pad(src: torch.Tensor, dst: torch.Tensor, N: int, h: int, w: int,
                                           _stream()), "seva_upsample2x_pad")
 
 
-def im2col3x3_s2(src: torch.Tensor, dst: torch.Tensor, N: int, h: int, w: int, Cc: int) -> None:
-    check(_lib.load().seva_im2col3x3_s2(src.data_ptr(), src.stride(0), dst.data_ptr(), N, h, w, Cc, _stream()),
-          "seva_im2col3x3_s2")
+def im2col3x3_s2(src: torch.Tensor, dst: torch.Tensor, N: int, h: int, w: int, Cc: int, origin: int = 0) -> None:
+    """``origin`` 0: symmetric pad 1 (Seva Downsample); 1: pad right / bottom only (the VAE's Downsample2D)."""
+    check(_lib.load().seva_im2col3x3_s2_at(src.data_ptr(), src.stride(0), dst.data_ptr(), N, h, w, Cc, origin,
+                                           _stream()), "seva_im2col3x3_s2_at")
+
+
+def softmax_rows(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp32 scores [rows, L] -> bf16 probabilities [rows, L]."""
+    _req(x, torch.float32, "x")
+    rows, L = x.shape
+    if out is None:
+        out = torch.empty((rows, L), device=x.device, dtype=torch.bfloat16)
+    check(_lib.load().seva_softmax_rows(x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), rows, L, _stream()),
+          "seva_softmax_rows")
+    return out
 
 
 def cast_bf16(src: torch.Tensor) -> torch.Tensor:
