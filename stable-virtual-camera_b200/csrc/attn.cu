@@ -24,6 +24,7 @@
 // the FMA pipe instead (Cody-Waite split + cubic, relative error 7.5e-5, far below the bf16 rounding of P).
 #include "common.cuh"
 #include <stdlib.h>
+#include <stdio.h>
 #include "../../include/seva_b200.h"
 
 namespace seva {
@@ -36,7 +37,8 @@ constexpr int kAttnCtrl = 1024;
 constexpr int kAttnSmem = kAttnCtrl + 1024 + (2 + kRing) * kTileBytes;
 constexpr int kRegsLow = 56;             // TMA / MMA / allocator warpgroup
 constexpr int kRegsHigh = 224;           // softmax warpgroups
-constexpr int kPingDefault = 0;          // exp-phase ping-pong between the two Q tiles' softmax warps
+constexpr bool kPingDefault = false;     // exp-phase token between the two Q tiles' softmax warps
+constexpr int kHalvesDefault = 1;        // P hand-offs per key block (1 = whole block, 2 = 64-key halves)
 constexpr int kEmuDefault = 4;           // pairs out of every 16 whose exp2 runs on the FMA pipe
 
 struct AttnArgs {
@@ -47,7 +49,17 @@ struct AttnArgs {
   // partial mode (keys split over several launches, seva_attn_partial): o is fp32 (ldo / bso in floats) and the
   // base-2 log-sum-exp of every (batch, head, query) over THIS launch's keys is written to lse
   float* lse;
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+  unsigned long long* trace;  // block (0,0,0): [warp role 0..4][iteration < 64][16 stamps]
+#endif
 };
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+#define TRACE(role, j, k)                                                                              \
+  if (a.trace != nullptr && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && (j) < 64 && lane == 0 && (role) >= 0) \
+    a.trace[((role) * 64 + (j)) * 16 + (k)] = clock64();
+#else
+#define TRACE(role, j, k)
+#endif
 
 // ---- packed fp32x2 helpers (FFMA2 / FADD2 on sm_100) ------------------------------------------
 __device__ __forceinline__ unsigned long long pack2f(float lo, float hi) {
@@ -104,8 +116,9 @@ __device__ __forceinline__ float ex2_pinned(float x) {
   asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// Named-barrier token that serialises the exponential phases of the two warps sharing an SM sub-partition (warp w of
-// Q tile 0 and warp w + 4 of Q tile 1): one is on the MUFU unit while the other loads S and reduces the row maximum.
+// Named-barrier token that alternates the exponential phases of the two warps sharing an SM sub-partition (warp w of
+// Q tile 0 and warp w + 4 of Q tile 1): one is on the MUFU unit while the other hands P over, loads the next S row and
+// reduces its maximum.  Left to themselves the two run in phase (MUFU saturated, then idle).
 __device__ __forceinline__ void token_wait(uint32_t id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void token_give(uint32_t id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
 
@@ -130,18 +143,22 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
   }
 }
 
-// One key block of the online softmax for this thread's row.
-template <bool kTail, int kEmu, bool kPing>
-__device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree,
+// One key block of the online softmax for this thread's row.  P leaves in two 64-key halves, each with its own
+// hand-off pair (bar_p / bar_pv + 8 * half), so that PV of the first half runs underneath the exponentials of the
+// second and the P columns of block j are only waited for right before block j + 1 overwrites them: the
+// exp(j) -> PV(j) -> exp(j + 1) chain of a single-buffered P is gone.
+template <bool kTail, int kEmu, int kHalves, bool kPing>
+__device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree, uint32_t bar_p,
                                              uint32_t bar_pv, float sl2, int kv_valid, int j, int lane,
-                                             uint32_t tok_mine, uint32_t tok_other, bool give,
-                                             float& m_run, float& l_run) {
+                                             uint32_t tok_mine, uint32_t tok_other, bool give, float& m_run, float& l_run, const AttnArgs& a, int role) {
   uint32_t s[128];
+  TRACE(role, j, 0)
   tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
   tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
   tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&s[64]));
   tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&s[96]));
   tmem_wait_ld();
+  TRACE(role, j, 1)
   // the row is in registers: give the S columns back so that S(j+1) runs underneath this softmax
   tc_fence_before();
   __syncwarp();
@@ -161,43 +178,62 @@ __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t 
   }
   const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
   const float m_new = fmaxf(m_run, mx * sl2);
+  TRACE(role, j, 2)
+  bool pv_done = (j == 0);  // both halves of PV(j-1) known complete
   if (j == 0) {
     m_run = m_new;
-  } else {
-    const bool need = m_new > m_run + 8.0f;
-    // O_i and P_i belong to the tensor pipe until PV_i(j-1) has completed
-    mbar_wait(bar_pv, (j - 1) & 1);
+  } else if (__any_sync(0xffffffffu, m_new > m_run + 8.0f)) {
+    // rare: O_i must be rescaled, and it belongs to the tensor pipe until PV_i(j-1) has completed
+    mbar_wait(bar_pv + 8 * (kHalves - 1), (j - 1) & 1);  // the last commit covers the earlier one
     tc_fence_after();
-    if (__any_sync(0xffffffffu, need)) {
-      const float alpha = fast_exp2(m_run - m_new);
-      l_run *= alpha;
-      m_run = m_new;
+    pv_done = true;
+    const float alpha = fast_exp2(m_run - m_new);
+    l_run *= alpha;
+    m_run = m_new;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t vo[16];
-        tmem_ld16(tO + c * 16, vo);
-        tmem_wait_ld();
+    for (int c = 0; c < 4; ++c) {
+      uint32_t vo[16];
+      tmem_ld16(tO + c * 16, vo);
+      tmem_wait_ld();
 #pragma unroll
-        for (int t = 0; t < 16; ++t) vo[t] = __float_as_uint(__uint_as_float(vo[t]) * alpha);
-        tmem_st16(tO + c * 16, vo);
-      }
+      for (int t = 0; t < 16; ++t) vo[t] = __float_as_uint(__uint_as_float(vo[t]) * alpha);
+      tmem_st16(tO + c * 16, vo);
     }
   }
   const unsigned long long sl2_2 = pack2f(sl2, sl2);
   const unsigned long long negm_2 = pack2f(-m_run, -m_run);
   unsigned long long sum2 = 0ull;
   if (kPing) token_wait(tok_mine);
+  TRACE(role, j, 3)
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     uint32_t pk[16];
     chunk_exp<kEmu, kPing>(&s[32 * c], sl2_2, negm_2, pk, sum2);
     if (kPing && c == 3 && give) token_give(tok_other);
+    if ((c == 0 || (kHalves == 2 && c == 2)) && !pv_done) {
+      // P columns of this half are read by PV_i(j-1) until its commit lands
+      mbar_wait(bar_pv + 8 * (c >> 1), (j - 1) & 1);
+      tc_fence_after();
+    }
     tmem_st16(tP + 16 * c, pk);
+    if (kHalves == 2 && c == 1) {
+      TRACE(role, j, 6)
+      tmem_wait_st();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p);
+    }
   }
   l_run += lo2f(sum2) + hi2f(sum2);
+  TRACE(role, j, 4)
+  tmem_wait_st();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar_p + 8 * (kHalves - 1));
+  TRACE(role, j, 5)
 }
 
-template <int kEmu, bool kPing>
+template <int kEmu, int kHalves, bool kPing>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -208,13 +244,15 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const uint32_t bar_empty = bar_full + 8 * kRing;   // kRing
   const uint32_t bar_s = bar_empty + 8 * kRing;      // 2
   const uint32_t bar_sfree = bar_s + 16;             // 2
-  const uint32_t bar_p = bar_sfree + 16;             // 2
-  const uint32_t bar_pv = bar_p + 16;                // 2
-  const uint32_t tmem_slot = bar_pv + 16;
+  const uint32_t bar_p = bar_sfree + 16;             // 2 tiles x 2 halves: + 16 * tile + 8 * half
+  const uint32_t bar_pv = bar_p + 32;                // 2 tiles x 2 halves
+  const uint32_t tmem_slot = bar_pv + 32;
   const uint32_t q_smem = smem_base + kAttnCtrl;           // 2 tiles
   const uint32_t ring_smem = q_smem + 2 * kTileBytes;      // kRing tiles
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role dispatch and every
+  // address / descriptor / ring cursor of the TMA and MMA warps in uniform registers (no R2UR in front of each UMMA)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 256;
   const int head = blockIdx.y;
@@ -233,8 +271,10 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s + 8 * i, 1);
       mbar_init(bar_sfree + 8 * i, 4);
-      mbar_init(bar_p + 8 * i, 4);
-      mbar_init(bar_pv + 8 * i, 1);
+      for (int h = 0; h < 2; ++h) {
+        mbar_init(bar_p + 16 * i + 8 * h, 4);
+        mbar_init(bar_pv + 16 * i + 8 * h, 1);
+      }
     }
     fence_barrier_init();
   }
@@ -290,12 +330,12 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         for (int k = 0; k < 4; ++k)
           umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
       };
-      auto issue_pv = [&](int i, uint32_t vaddr, int j) {
+      auto issue_pv = [&](int i, int half, uint64_t vdesc, int j) {
+        constexpr int kPer = 8 / kHalves;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart; P columns advance by 8
-          const uint64_t vdesc = make_sdesc_sw128(vaddr + k * 2048, 8192, 1024);
-          umma_ts(tmem_base + 256 + i * 64, tmem_base + 384 + i * 64 + k * 8, vdesc, idesc_pv,
+        for (int k = kPer * half; k < kPer * half + kPer; ++k) {
+          // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart (128 descriptor units); P columns advance by 8
+          umma_ts(tmem_base + 256 + i * 64, tmem_base + 384 + i * 64 + k * 8, vdesc + uint64_t(k * 128), idesc_pv,
                   (j | k) != 0 ? 1u : 0u);
         }
       };
@@ -313,44 +353,53 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       __syncwarp();
       ring_next();
       for (int j = 0; j < nkv; ++j) {
+        TRACE(2, j, 0)
         if (j + 1 < nkv) {
           // S_i(j+1) as soon as softmax_i has pulled S_i(j) into registers
           mbar_wait(bar_full + 8 * rs, rph);
+          TRACE(2, j, 1)
           const uint32_t kaddr = ring_smem + rs * kTileBytes;
           mbar_wait(bar_sfree, j & 1);
           tc_fence_after();
+          TRACE(2, j, 2)
           if (elect_one()) {
             issue_s(0, kaddr);
             tc_commit(bar_s);
           }
           __syncwarp();
+          TRACE(2, j, 3)
           mbar_wait(bar_sfree + 8, j & 1);
           tc_fence_after();
+          TRACE(2, j, 4)
           if (elect_one()) {
             issue_s(1, kaddr);
             tc_commit(bar_s + 8);
             tc_commit(bar_empty + 8 * rs);
           }
           __syncwarp();
+          TRACE(2, j, 5)
           ring_next();
         }
         mbar_wait(bar_full + 8 * rs, rph);
-        const uint32_t vaddr = ring_smem + rs * kTileBytes;
-        mbar_wait(bar_p, j & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          issue_pv(0, vaddr, j);
-          tc_commit(bar_pv);
+        TRACE(2, j, 6)
+        const uint64_t vdesc = make_sdesc_sw128(ring_smem + rs * kTileBytes, 8192, 1024);
+        // PV in the order the softmax warps hand the halves over: (tile 0, tile 1) x (keys 0-63, keys 64-127)
+#pragma unroll
+        for (int half = 0; half < kHalves; ++half) {
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            mbar_wait(bar_p + 16 * i + 8 * half, j & 1);
+            tc_fence_after();
+            TRACE(2, j, 7 + 2 * (i + 2 * half))
+            if (elect_one()) {
+              issue_pv(i, half, vdesc, j);
+              tc_commit(bar_pv + 16 * i + 8 * half);
+              if (half == kHalves - 1 && i == 1) tc_commit(bar_empty + 8 * rs);
+            }
+            __syncwarp();
+            TRACE(2, j, 8 + 2 * (i + 2 * half))
+          }
         }
-        __syncwarp();
-        mbar_wait(bar_p + 8, j & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          issue_pv(1, vaddr, j);
-          tc_commit(bar_pv + 8);
-          tc_commit(bar_empty + 8 * rs);
-        }
-        __syncwarp();
         ring_next();
       }
     }
@@ -369,24 +418,22 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     float l_run = 0.0f;
     const uint32_t tok_mine = 1 + 2 * quarter + i, tok_other = 1 + 2 * quarter + (i ^ 1);
     if (kPing && i == 1) token_give(tok_other);  // tile 0 takes the first turn
+    const int trole = quarter == 0 ? i : (quarter == 1 ? 3 + i : -1);
+    (void)trole;
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(bar_s + 8 * i, j & 1);
       tc_fence_after();
       const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
       if (kv_valid >= 128)
-        softmax_step<false, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, 128, j, lane, tok_mine,
-                                         tok_other, i == 0 || j + 1 < nkv, m_run, l_run);
+        softmax_step<false, kEmu, kHalves, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i, bar_pv + 16 * i, sl2, 128, j,
+                                                  lane, tok_mine, tok_other, i == 0 || j + 1 < nkv, m_run, l_run, a, trole);
       else
-        softmax_step<true, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_pv + 8 * i, sl2, kv_valid, j, lane, tok_mine,
-                                        tok_other, i == 0 || j + 1 < nkv, m_run, l_run);
-      tmem_wait_st();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p + 8 * i);
+        softmax_step<true, kEmu, kHalves, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i, bar_pv + 16 * i, sl2, kv_valid,
+                                                 j, lane, tok_mine, tok_other, i == 0 || j + 1 < nkv, m_run, l_run, a, trole);
     }
 
     // epilogue: O_i / l -> bf16 -> global
-    mbar_wait(bar_pv + 8 * i, (nkv - 1) & 1);
+    mbar_wait(bar_pv + 16 * i + 8 * (kHalves - 1), (nkv - 1) & 1);  // the last commit covers the earlier one
     tc_fence_after();
     const int qrow = q0 + i * 128 + row;
     const float inv_l = 1.0f / l_run;
@@ -550,37 +597,59 @@ static int attn_launch(const void* q, const void* k, const void* v, void* o, flo
   a.bso = bso;
   a.scale_log2 = scale * 1.4426950408889634f;
   a.lse = lse;
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+  static unsigned long long* trace_dev = nullptr;
+  const char* trace_path = getenv("SEVA_ATTN_TRACE_FILE");
+  if (trace_path && !trace_dev) cudaMalloc(&trace_dev, 5 * 64 * 16 * 8);
+  if (trace_dev) cudaMemset(trace_dev, 0, 5 * 64 * 16 * 8);
+  a.trace = trace_path ? trace_dev : nullptr;
+#endif
   dim3 grid((Lq + 255) / 256, Hh, B);
-#define SEVA_ATTN_LAUNCH(E, P)                                                                      \
+#define SEVA_ATTN_LAUNCH(E, H, P)                                                                   \
   {                                                                                                 \
-    if (ensure_dyn_smem(reinterpret_cast<const void*>(attn_kernel<E, P>), kAttnSmem)) return 2;     \
-    attn_kernel<E, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);                 \
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(attn_kernel<E, H, P>), kAttnSmem)) return 2;  \
+    attn_kernel<E, H, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);              \
   }
 #ifdef SEVA_DEBUG
-  // developer builds only: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_PING = 0 / 1
+  // developer builds only: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_HALVES = 1, 2,
+  // SEVA_ATTN_PING = 0, 1
   static const int emu = [] { const char* e = getenv("SEVA_ATTN_EMU"); return e ? atoi(e) : kEmuDefault; }();
-  static const int ping = [] { const char* e = getenv("SEVA_ATTN_PING"); return e ? atoi(e) : kPingDefault; }();
-  if (ping) {
-    switch (emu) {
-      case 0: SEVA_ATTN_LAUNCH(0, true) break;
-      case 2: SEVA_ATTN_LAUNCH(2, true) break;
-      case 6: SEVA_ATTN_LAUNCH(6, true) break;
-      case 8: SEVA_ATTN_LAUNCH(8, true) break;
-      default: SEVA_ATTN_LAUNCH(4, true) break;
-    }
-  } else {
-    switch (emu) {
-      case 0: SEVA_ATTN_LAUNCH(0, false) break;
-      case 2: SEVA_ATTN_LAUNCH(2, false) break;
-      case 6: SEVA_ATTN_LAUNCH(6, false) break;
-      case 8: SEVA_ATTN_LAUNCH(8, false) break;
-      default: SEVA_ATTN_LAUNCH(4, false) break;
-    }
+  static const int halves = [] { const char* e = getenv("SEVA_ATTN_HALVES"); return e ? atoi(e) : kHalvesDefault; }();
+  static const int ping = [] { const char* e = getenv("SEVA_ATTN_PING"); return e ? atoi(e) : (kPingDefault ? 1 : 0); }();
+#define SEVA_ATTN_EMU_SWITCH(H, P)                 \
+  switch (emu) {                                   \
+    case 0: SEVA_ATTN_LAUNCH(0, H, P) break;       \
+    case 2: SEVA_ATTN_LAUNCH(2, H, P) break;       \
+    case 6: SEVA_ATTN_LAUNCH(6, H, P) break;       \
+    case 8: SEVA_ATTN_LAUNCH(8, H, P) break;       \
+    default: SEVA_ATTN_LAUNCH(4, H, P) break;      \
   }
+  if (halves == 2 && ping) SEVA_ATTN_EMU_SWITCH(2, true)
+  else if (halves == 2) SEVA_ATTN_EMU_SWITCH(2, false)
+  else if (ping) SEVA_ATTN_EMU_SWITCH(1, true)
+  else SEVA_ATTN_EMU_SWITCH(1, false)
+#undef SEVA_ATTN_EMU_SWITCH
 #else
-  SEVA_ATTN_LAUNCH(kEmuDefault, (kPingDefault != 0))  // the one release instantiation
+  SEVA_ATTN_LAUNCH(kEmuDefault, kHalvesDefault, kPingDefault)  // the one release instantiation
 #endif
 #undef SEVA_ATTN_LAUNCH
   SEVA_CUDA(cudaGetLastError());
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+  if (a.trace) {
+    static unsigned long long host[5 * 64 * 16];
+    cudaDeviceSynchronize();
+    cudaMemcpy(host, trace_dev, sizeof(host), cudaMemcpyDeviceToHost);
+    FILE* f = fopen(trace_path, "w");
+    if (f) {
+      for (int r = 0; r < 5; ++r)
+        for (int j = 0; j < 64; ++j) {
+          fprintf(f, "%d %d", r, j);
+          for (int k = 0; k < 16; ++k) fprintf(f, " %llu", host[(r * 64 + j) * 16 + k]);
+          fprintf(f, "\n");
+        }
+      fclose(f);
+    }
+  }
+#endif
   return 0;
 }
