@@ -7,18 +7,23 @@
 //
 // One CTA owns two 128-row Q tiles of one (batch, head) and streams K/V tiles of 128 keys:
 //   warp 0       TMA producer: Q0, Q1 once; K_j / V_j through an 8-entry ring of 16 KB tiles
-//   warp 1       MMA issuer:   S_i = Q_i K_j^T  (SS, 128x128x64)  and  O_i += P_i V_j (TS, 128x64x128)
+//   warp 1       MMA issuer:   S_i = Q_i K_j^T  (SS, 128x128x64)  and  O_i += P_i V_j (TS, two 128x64x64 halves)
 //   warp 2       TMEM allocator
-//   warps 4-7    softmax for Q tile 0: one thread per row; the whole 128-column S row is pulled into
-//   warps 8-11   softmax for Q tile 1  registers in one pass (224 registers per thread via setmaxnreg), so
-//                the S columns are handed back to the tensor pipe BEFORE the exponentials start and
-//                S_i(j+1) is computed underneath softmax_i(j).  P goes to its own TMEM columns.
+//   warps 4-19   softmax: warp 4 + 8 * half + 4 * tile + quarter owns rows [32 * quarter, +32) of Q tile `tile` and the
+//                key columns [64 * half, +64) of every S block, i.e. TWO threads per row.  Four softmax warps per SM
+//                sub-partition instead of two: the clock64 trace of the one-thread-per-row kernel (profiles/r2j) showed
+//                each warp's exp phase at ~1250 clk for 768 MUFU clk -- a single warp cannot issue its ~480
+//                instructions per block any faster -- with the MUFU unit idle 40 % of the time.  The two threads of a
+//                row exchange their block maximum through shared memory (one 64-thread named barrier per row group).
+//                S columns are handed back to the tensor pipe as soon as they are in registers, so S_i(j+1) runs
+//                underneath softmax_i(j).  P goes to its own TMEM columns, in two 64-key halves with their own hand-offs
+//                (half h is written by the `half == h` warps), so PV of one half never waits for the other.
 // TMEM columns: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512)  (P is bf16).
 // Per (tile i, key block j) hand-offs, all mbarriers with phase j & 1:
-//   bar_s[i]      MMA -> softmax   S_i(j) complete                      (tcgen05.commit)
-//   bar_sfree[i]  softmax -> MMA   S_i(j) is in registers               (one arrival per warp)
-//   bar_p[i]      softmax -> MMA   P_i(j) is in TMEM                    (one arrival per warp)
-//   bar_pv[i]     MMA -> softmax   O_i += P_i(j) V_j complete: P_i and O_i may be touched again
+//   bar_s[i]        MMA -> softmax   S_i(j) complete                        (tcgen05.commit)
+//   bar_sfree[i]    softmax -> MMA   S_i(j) is in registers                 (one arrival per warp: 8)
+//   bar_p[i][h]     softmax -> MMA   half h of P_i(j) is in TMEM            (one arrival per warp: 4)
+//   bar_pv[i][h]    MMA -> softmax   O_i += P_i(j)[:, h] V_j[h] complete: that half of P_i may be overwritten
 // The MUFU unit (16 ex2/clk/SM) is the ceiling of this kernel at head dim 64 (128x128 exponentials
 // against 512 tensor-pipe clocks per tile pair), so a fixed fraction of the exponentials is evaluated on
 // the FMA pipe instead (Cody-Waite split + cubic, relative error 7.5e-5, far below the bf16 rounding of P).
@@ -30,15 +35,15 @@
 namespace seva {
 namespace {
 
-constexpr int kAttnThreads = 384;
+constexpr int kAttnThreads = 640;       // 4 service warps + 16 softmax warps
 constexpr int kRing = 8;                 // K/V ring entries (16 KB each)
 constexpr int kTileBytes = 128 * 64 * 2; // 16 KB
-constexpr int kAttnCtrl = 1024;
-constexpr int kAttnSmem = kAttnCtrl + 1024 + (2 + kRing) * kTileBytes;
+constexpr int kAttnCtrl = 1024;          // mbarriers + TMEM slot
+constexpr int kAttnXchg = 4096;          // row maxima / row sums between the two threads of a row: [2][2 tiles][128][2] fp32
+constexpr int kAttnSmem = kAttnCtrl + kAttnXchg + 1024 + (2 + kRing) * kTileBytes;
 constexpr int kRegsLow = 56;             // TMA / MMA / allocator warpgroup
-constexpr int kRegsHigh = 224;           // softmax warpgroups
-constexpr bool kPingDefault = false;     // exp-phase token between the two Q tiles' softmax warps
-constexpr int kHalvesDefault = 1;        // P hand-offs per key block (1 = whole block, 2 = 64-key halves)
+constexpr int kRegsHigh = 104;           // softmax warps: the CTA is launched with 640 x 96 = 61440 registers; 512 x 104 + 128 x 56 = 60416
+constexpr bool kPingDefault = false;     // exp-phase token between the two Q tiles
 constexpr int kEmuDefault = 4;           // pairs out of every 16 whose exp2 runs on the FMA pipe
 
 struct AttnArgs {
@@ -57,6 +62,27 @@ struct AttnArgs {
 #define TRACE(role, j, k)                                                                              \
   if (a.trace != nullptr && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && (j) < 64 && lane == 0 && (role) >= 0) \
     a.trace[((role) * 64 + (j)) * 16 + (k)] = clock64();
+// first timed-out mbarrier wait of the launch: {source line, barrier smem address, parity, block x|y<<10|z<<20, warp, base}
+__device__ unsigned int g_attn_timeout[8];
+__device__ __forceinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int line) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 17)) {
+      if ((threadIdx.x & 31) == 0 && atomicCAS(&g_attn_timeout[0], 0u, (unsigned)line) == 0u) {
+        g_attn_timeout[1] = bar;
+        g_attn_timeout[2] = parity;
+        g_attn_timeout[3] = blockIdx.x | (blockIdx.y << 10) | (blockIdx.z << 20);
+        g_attn_timeout[4] = threadIdx.x >> 5;
+        extern __shared__ uint8_t smem_raw_dbg[];
+        g_attn_timeout[5] = (smem_u32(smem_raw_dbg) + 1023u) & ~1023u;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(g_attn_timeout[6]) : "r"(g_attn_timeout[5] + 512));
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(g_attn_timeout[7]) : "r"(g_attn_timeout[5] + 516));
+      }
+      return;  // carry on with garbage so that the kernel ends and the host can print the record
+    }
+  }
+}
+#define mbar_wait(bar, parity) mbar_wait_dbg(bar, parity, __LINE__)
 #else
 #define TRACE(role, j, k)
 #endif
@@ -110,19 +136,23 @@ __device__ __forceinline__ unsigned long long exp2_poly2(unsigned long long x2) 
   return pack2u(r0, r1);
 }
 
+__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+
 // ex2 that keeps its place relative to the exp-phase token (volatile asm statements are not reordered among themselves)
 __device__ __forceinline__ float ex2_pinned(float x) {
   float y;
   asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// Named-barrier token that alternates the exponential phases of the two warps sharing an SM sub-partition (warp w of
-// Q tile 0 and warp w + 4 of Q tile 1): one is on the MUFU unit while the other hands P over, loads the next S row and
-// reduces its maximum.  Left to themselves the two run in phase (MUFU saturated, then idle).
-__device__ __forceinline__ void token_wait(uint32_t id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
-__device__ __forceinline__ void token_give(uint32_t id) { asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory"); }
+// Exp-phase token between the two Q tiles (named barriers 9 / 10, 8 waiting + 8 arriving warps): the tiles' softmax
+// warps share the four MUFU units, and left to themselves they run in phase -- MUFU saturated during both exp phases,
+// idle while both load S, reduce maxima and wait for the tensor pipe.  With the token tile 0 is on the MUFU units while
+// tile 1 does everything else, and vice versa.
+__device__ __forceinline__ void token_wait(uint32_t id) { asm volatile("bar.sync %0, 512;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void token_give(uint32_t id) { asm volatile("bar.arrive %0, 512;" ::"r"(id) : "memory"); }
 
-__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+// 64-thread named barrier of one row group: the `half == 0` and `half == 1` warps that share 32 rows
+__device__ __forceinline__ void pair_sync(uint32_t id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 
 // P chunk = exp2(s * scale_log2 - m) for 32 columns -> 16 packed bf16x2; accumulates the row sum
 template <int kEmu, bool kPin>
@@ -143,55 +173,63 @@ __device__ __forceinline__ void chunk_exp(const uint32_t* v, unsigned long long 
   }
 }
 
-// One key block of the online softmax for this thread's row.  P leaves in two 64-key halves, each with its own
-// hand-off pair (bar_p / bar_pv + 8 * half), so that PV of the first half runs underneath the exponentials of the
-// second and the P columns of block j are only waited for right before block j + 1 overwrites them: the
-// exp(j) -> PV(j) -> exp(j + 1) chain of a single-buffered P is gone.
-template <bool kTail, int kEmu, int kHalves, bool kPing>
+// One key block of the online softmax for this thread's half row (64 key columns).
+//   tS / tP     this thread's 64 S columns / 32 P columns          tO   this thread's 32 O columns (rescale only)
+//   xch         shared-memory slot pair of this row for block parity j & 1: [mine, other's]
+//   bar_p / bar_pv   hand-offs of THIS half;  bar_pv_other  the other half's PV completion (rescale only)
+template <bool kTail, int kEmu, bool kPing>
 __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t tP, uint32_t bar_sfree, uint32_t bar_p,
-                                             uint32_t bar_pv, float sl2, int kv_valid, int j, int lane,
-                                             uint32_t tok_mine, uint32_t tok_other, bool give, float& m_run, float& l_run, const AttnArgs& a, int role) {
-  uint32_t s[128];
+                                             uint32_t bar_pv, uint32_t bar_pv_other, uint32_t xch_mine,
+                                             uint32_t xch_other, uint32_t pair_bar, uint32_t tok_mine,
+                                             uint32_t tok_other, bool give, float sl2, int kv_valid, int j,
+                                             int lane, float& m_run, float& l_run, const AttnArgs& a, int role) {
+  uint32_t s[64];
   TRACE(role, j, 0)
   tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
   tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
-  tmem_ld32(tS + 64, *reinterpret_cast<uint32_t(*)[32]>(&s[64]));
-  tmem_ld32(tS + 96, *reinterpret_cast<uint32_t(*)[32]>(&s[96]));
   tmem_wait_ld();
   TRACE(role, j, 1)
-  // the row is in registers: give the S columns back so that S(j+1) runs underneath this softmax
+  // the half row is in registers: give the S columns back so that S(j+1) runs underneath this softmax
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive(bar_sfree);
   if (kTail) {
 #pragma unroll
-    for (int c = 0; c < 128; ++c)
+    for (int c = 0; c < 64; ++c)
       if (c >= kv_valid) s[c] = 0xff800000u;  // -inf: exp2 gives 0
   }
   float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-  for (int c = 0; c < 128; c += 8) {
+  for (int c = 0; c < 64; c += 8) {
     m0 = max3(m0, __uint_as_float(s[c + 0]), __uint_as_float(s[c + 1]));
     m1 = max3(m1, __uint_as_float(s[c + 2]), __uint_as_float(s[c + 3]));
     m2 = max3(m2, __uint_as_float(s[c + 4]), __uint_as_float(s[c + 5]));
     m3 = max3(m3, __uint_as_float(s[c + 6]), __uint_as_float(s[c + 7]));
   }
-  const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-  const float m_new = fmaxf(m_run, mx * sl2);
+  const float mx_mine = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+  // block maximum of the whole row: exchange with the thread that owns the other 64 columns
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(xch_mine), "f"(mx_mine) : "memory");
+  pair_sync(pair_bar);
+  float mx_other;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(mx_other) : "r"(xch_other) : "memory");
+  const float m_new = fmaxf(m_run, fmaxf(mx_mine, mx_other) * sl2);
   TRACE(role, j, 2)
-  bool pv_done = (j == 0);  // both halves of PV(j-1) known complete
+  bool pv_done = (j == 0);  // PV(j-1) of this half known complete
   if (j == 0) {
     m_run = m_new;
   } else if (__any_sync(0xffffffffu, m_new > m_run + 8.0f)) {
-    // rare: O_i must be rescaled, and it belongs to the tensor pipe until PV_i(j-1) has completed
-    mbar_wait(bar_pv + 8 * (kHalves - 1), (j - 1) & 1);  // the last commit covers the earlier one
+    // rare: O_i must be rescaled (both threads of a row take the same decision: same m_run, same m_new), and O_i
+    // belongs to the tensor pipe until both halves of PV_i(j-1) have completed.  Each thread scales its 32 columns;
+    // neither half of P_i(j) may be handed over before BOTH threads' columns are rescaled.
+    mbar_wait(bar_pv, (j - 1) & 1);
+    mbar_wait(bar_pv_other, (j - 1) & 1);
     tc_fence_after();
     pv_done = true;
     const float alpha = fast_exp2(m_run - m_new);
     l_run *= alpha;
     m_run = m_new;
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < 2; ++c) {
       uint32_t vo[16];
       tmem_ld16(tO + c * 16, vo);
       tmem_wait_ld();
@@ -199,6 +237,10 @@ __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t 
       for (int t = 0; t < 16; ++t) vo[t] = __float_as_uint(__uint_as_float(vo[t]) * alpha);
       tmem_st16(tO + c * 16, vo);
     }
+    tmem_wait_st();
+    tc_fence_before();
+    pair_sync(pair_bar);
+    tc_fence_after();
   }
   const unsigned long long sl2_2 = pack2f(sl2, sl2);
   const unsigned long long negm_2 = pack2f(-m_run, -m_run);
@@ -206,34 +248,27 @@ __device__ __forceinline__ void softmax_step(uint32_t tS, uint32_t tO, uint32_t 
   if (kPing) token_wait(tok_mine);
   TRACE(role, j, 3)
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < 2; ++c) {
     uint32_t pk[16];
     chunk_exp<kEmu, kPing>(&s[32 * c], sl2_2, negm_2, pk, sum2);
-    if (kPing && c == 3 && give) token_give(tok_other);
-    if ((c == 0 || (kHalves == 2 && c == 2)) && !pv_done) {
-      // P columns of this half are read by PV_i(j-1) until its commit lands
-      mbar_wait(bar_pv + 8 * (c >> 1), (j - 1) & 1);
+    if (kPing && c == 1 && give) token_give(tok_other);
+    if (c == 0 && !pv_done) {
+      // this half of the P columns is read by PV_i(j-1) until its commit lands
+      mbar_wait(bar_pv, (j - 1) & 1);
       tc_fence_after();
     }
     tmem_st16(tP + 16 * c, pk);
-    if (kHalves == 2 && c == 1) {
-      TRACE(role, j, 6)
-      tmem_wait_st();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p);
-    }
   }
   l_run += lo2f(sum2) + hi2f(sum2);
   TRACE(role, j, 4)
   tmem_wait_st();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(bar_p + 8 * (kHalves - 1));
+  if (lane == 0) mbar_arrive(bar_p);
   TRACE(role, j, 5)
 }
 
-template <int kEmu, int kHalves, bool kPing>
+template <int kEmu, bool kPing>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnArgs a) {
@@ -247,7 +282,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const uint32_t bar_p = bar_sfree + 16;             // 2 tiles x 2 halves: + 16 * tile + 8 * half
   const uint32_t bar_pv = bar_p + 32;                // 2 tiles x 2 halves
   const uint32_t tmem_slot = bar_pv + 32;
-  const uint32_t q_smem = smem_base + kAttnCtrl;           // 2 tiles
+  const uint32_t xchg = smem_base + kAttnCtrl;             // [parity][tile][row][half] fp32
+  const uint32_t q_smem = xchg + kAttnXchg;                // 2 tiles
   const uint32_t ring_smem = q_smem + 2 * kTileBytes;      // kRing tiles
 
   // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role dispatch and every
@@ -270,7 +306,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_s + 8 * i, 1);
-      mbar_init(bar_sfree + 8 * i, 4);
+      mbar_init(bar_sfree + 8 * i, 8);
       for (int h = 0; h < 2; ++h) {
         mbar_init(bar_p + 16 * i + 8 * h, 4);
         mbar_init(bar_pv + 16 * i + 8 * h, 1);
@@ -299,7 +335,11 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       // ring order = the order in which the MMA warp consumes and frees the tiles: K0, then per key block j
       // [K(j+1)], V(j)
       uint32_t s = 0, ph = 0;
+      uint32_t seq_dbg = 0;
       auto load = [&](const CUtensorMap* tm, int j) {
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+        if (lane == 0) asm volatile("st.shared.b32 [%0], %1;" ::"r"(smem_base + 516), "r"(seq_dbg++));
+#endif
         mbar_wait(bar_empty + 8 * s, ph ^ 1);
         if (elect_one()) {
           mbar_expect_tx(bar_full + 8 * s, kTileBytes);
@@ -321,150 +361,167 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major (d contiguous)
       const uint64_t qdesc0 = make_sdesc_sw128(q_smem, 16, 1024);
       const uint64_t qdesc1 = make_sdesc_sw128(q_smem + kTileBytes, 16, 1024);
-      uint32_t rs = 0, rph = 0;  // ring cursor
-      auto ring_next = [&]() { if (++rs == kRing) { rs = 0; rph ^= 1; } };
-      auto issue_s = [&](int i, uint32_t kaddr) {
-        const uint64_t kdesc = make_sdesc_sw128(kaddr, 16, 1024);
+      auto issue_s = [&](int i, uint64_t kdesc) {
         const uint64_t qd = i ? qdesc1 : qdesc0;
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           umma_ss(tmem_base + i * 128, qd + 2 * k, kdesc + 2 * k, idesc_qk, k != 0 ? 1u : 0u);
       };
       auto issue_pv = [&](int i, int half, uint64_t vdesc, int j) {
-        constexpr int kPer = 8 / kHalves;
 #pragma unroll
-        for (int k = kPer * half; k < kPer * half + kPer; ++k) {
+        for (int k = 4 * half; k < 4 * half + 4; ++k) {
           // 16 keys per step: V rows [16k, 16k+16) start 2048 B apart (128 descriptor units); P columns advance by 8
           umma_ts(tmem_base + 256 + i * 64, tmem_base + 384 + i * 64 + k * 8, vdesc + uint64_t(k * 128), idesc_pv,
                   (j | k) != 0 ? 1u : 0u);
         }
       };
 
+      // Ring positions (the producer's order K0, K1, V0, K2, V1, ...): K(j) at 2j - 1 (K0 at 0), V(j) at 2j + 2
+      // (the last V one earlier: no K tile is loaded after the last block).
+      auto slot_of = [&](int pos) { return uint32_t(pos) & (kRing - 1); };
+      auto phase_of = [&](int pos) { return (uint32_t(pos) / kRing) & 1u; };
       mbar_wait(bar_q, 0);
-      mbar_wait(bar_full + 8 * rs, rph);
+      mbar_wait(bar_full, 0);
       tc_fence_after();
       if (elect_one()) {
-        issue_s(0, ring_smem + rs * kTileBytes);
+        const uint64_t kdesc = make_sdesc_sw128(ring_smem, 16, 1024);
+        issue_s(0, kdesc);
         tc_commit(bar_s);
-        issue_s(1, ring_smem + rs * kTileBytes);
+        issue_s(1, kdesc);
         tc_commit(bar_s + 8);
-        tc_commit(bar_empty + 8 * rs);
+        tc_commit(bar_empty);
       }
       __syncwarp();
-      ring_next();
+      // Issue order = the order in which the two tiles, half a block apart under the exp-phase token, hand things over:
+      //   PV_0(j-1)   S_0(j+1)   PV_1(j-1)   S_1(j+1)
+      auto do_pv = [&](int i, int jj) {
+        const int pos = 2 * jj + 2 - (jj + 1 >= nkv ? 1 : 0);  // no K tile follows the last block
+        const uint32_t sl = slot_of(pos);
+        if (i == 0) mbar_wait(bar_full + 8 * sl, phase_of(pos));
+        const uint64_t vdesc = make_sdesc_sw128(ring_smem + sl * kTileBytes, 8192, 1024);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          mbar_wait(bar_p + 16 * i + 8 * half, jj & 1);
+          tc_fence_after();
+          TRACE(2, jj, 1 + 4 * i + half)
+          if (elect_one()) {
+            issue_pv(i, half, vdesc, jj);
+            tc_commit(bar_pv + 16 * i + 8 * half);
+            if (half == 1 && i == 1) tc_commit(bar_empty + 8 * sl);
+          }
+          __syncwarp();
+        }
+      };
+      auto do_s = [&](int i, int jn) {   // S_i(jn), jn >= 1
+        const int pos = 2 * jn - 1;
+        const uint32_t sl = slot_of(pos);
+        if (i == 0) mbar_wait(bar_full + 8 * sl, phase_of(pos));
+        const uint64_t kdesc = make_sdesc_sw128(ring_smem + sl * kTileBytes, 16, 1024);
+        mbar_wait(bar_sfree + 8 * i, (jn - 1) & 1);
+        tc_fence_after();
+        TRACE(2, jn - 1, 3 + 4 * i)
+        if (elect_one()) {
+          issue_s(i, kdesc);
+          tc_commit(bar_s + 8 * i);
+          if (i == 1) tc_commit(bar_empty + 8 * sl);
+        }
+        __syncwarp();
+      };
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_ORDER_SSPP)
       for (int j = 0; j < nkv; ++j) {
-        TRACE(2, j, 0)
-        if (j + 1 < nkv) {
-          // S_i(j+1) as soon as softmax_i has pulled S_i(j) into registers
-          mbar_wait(bar_full + 8 * rs, rph);
-          TRACE(2, j, 1)
-          const uint32_t kaddr = ring_smem + rs * kTileBytes;
-          mbar_wait(bar_sfree, j & 1);
-          tc_fence_after();
-          TRACE(2, j, 2)
-          if (elect_one()) {
-            issue_s(0, kaddr);
-            tc_commit(bar_s);
-          }
-          __syncwarp();
-          TRACE(2, j, 3)
-          mbar_wait(bar_sfree + 8, j & 1);
-          tc_fence_after();
-          TRACE(2, j, 4)
-          if (elect_one()) {
-            issue_s(1, kaddr);
-            tc_commit(bar_s + 8);
-            tc_commit(bar_empty + 8 * rs);
-          }
-          __syncwarp();
-          TRACE(2, j, 5)
-          ring_next();
-        }
-        mbar_wait(bar_full + 8 * rs, rph);
-        TRACE(2, j, 6)
-        const uint64_t vdesc = make_sdesc_sw128(ring_smem + rs * kTileBytes, 8192, 1024);
-        // PV in the order the softmax warps hand the halves over: (tile 0, tile 1) x (keys 0-63, keys 64-127)
-#pragma unroll
-        for (int half = 0; half < kHalves; ++half) {
-#pragma unroll
-          for (int i = 0; i < 2; ++i) {
-            mbar_wait(bar_p + 16 * i + 8 * half, j & 1);
-            tc_fence_after();
-            TRACE(2, j, 7 + 2 * (i + 2 * half))
-            if (elect_one()) {
-              issue_pv(i, half, vdesc, j);
-              tc_commit(bar_pv + 16 * i + 8 * half);
-              if (half == kHalves - 1 && i == 1) tc_commit(bar_empty + 8 * rs);
-            }
-            __syncwarp();
-            TRACE(2, j, 8 + 2 * (i + 2 * half))
-          }
-        }
-        ring_next();
+#if defined(SEVA_ATTN_TRACE)
+        if (lane == 0) asm volatile("st.shared.b32 [%0], %1;" ::"r"(smem_base + 512), "r"(j));
+#endif
+        if (j + 1 < nkv) do_s(0, j + 1);
+        if (j + 1 < nkv) do_s(1, j + 1);
+        do_pv(0, j);
+        do_pv(1, j);
       }
+#else
+      for (int j = 0; j <= nkv; ++j) {
+        TRACE(2, j, 0)
+        if (j > 0) do_pv(0, j - 1);
+        if (j + 1 < nkv) do_s(0, j + 1);
+        if (j > 0) do_pv(1, j - 1);
+        if (j + 1 < nkv) do_s(1, j + 1);
+      }
+#endif
     }
   } else {
     // ------------------------------------ softmax + epilogue ------------------------------------
     setmaxnreg_inc<kRegsHigh>();
-    const int i = (warp - 4) >> 2;     // Q tile handled by this warpgroup
-    const int quarter = warp & 3;      // TMEM lane quarter
+    const int sw = warp - 4;
+    const int quarter = sw & 3;        // TMEM lane quarter (= warp % 4)
+    const int i = (sw >> 2) & 1;       // Q tile
+    const int half = sw >> 3;          // key-column half of every S block
     const int row = quarter * 32 + lane;
     const uint32_t lane_sel = uint32_t(quarter * 32) << 16;
-    const uint32_t tS = tmem_base + lane_sel + i * 128;
-    const uint32_t tO = tmem_base + lane_sel + 256 + i * 64;
-    const uint32_t tP = tmem_base + lane_sel + 384 + i * 64;
+    const uint32_t tS = tmem_base + lane_sel + i * 128 + half * 64;
+    const uint32_t tO = tmem_base + lane_sel + 256 + i * 64 + half * 32;
+    const uint32_t tP = tmem_base + lane_sel + 384 + i * 64 + half * 32;
+    const uint32_t pair_bar = 1 + i * 4 + quarter;
+    const uint32_t xch_row = xchg + uint32_t((i * 128 + row) * 8);   // + 2048 * parity; [mine at 4 * half]
     const float sl2 = a.scale_log2;
     float m_run = -INFINITY;  // running max of s*scale*log2(e) (possibly stale by < 8)
-    float l_run = 0.0f;
-    const uint32_t tok_mine = 1 + 2 * quarter + i, tok_other = 1 + 2 * quarter + (i ^ 1);
-    if (kPing && i == 1) token_give(tok_other);  // tile 0 takes the first turn
-    const int trole = quarter == 0 ? i : (quarter == 1 ? 3 + i : -1);
+    float l_run = 0.0f;       // this thread's share of the row sum
+    if (kPing && i == 1) token_give(9);  // tile 0 takes the first turn on the MUFU units
+    const int trole = quarter == 0 ? i + 3 * half : -1;
     (void)trole;
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(bar_s + 8 * i, j & 1);
       tc_fence_after();
-      const int kv_valid = a.Lk - j * 128;  // < 128 only on the tail tile
-      if (kv_valid >= 128)
-        softmax_step<false, kEmu, kHalves, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i, bar_pv + 16 * i, sl2, 128, j,
-                                                  lane, tok_mine, tok_other, i == 0 || j + 1 < nkv, m_run, l_run, a, trole);
+      const int kv_valid = a.Lk - j * 128 - half * 64;  // valid columns among this thread's 64; < 64 only on the tail tile
+      const uint32_t xr = xch_row + uint32_t((j & 1) * 2048);
+      if (kv_valid >= 64)
+        softmax_step<false, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i + 8 * half,
+                                         bar_pv + 16 * i + 8 * half, bar_pv + 16 * i + 8 * (half ^ 1), xr + 4 * half,
+                                         xr + 4 * (half ^ 1), pair_bar, 9 + i, 9 + (i ^ 1), i == 0 || j + 1 < nkv, sl2, 64, j,
+                                         lane, m_run, l_run, a, trole);
       else
-        softmax_step<true, kEmu, kHalves, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i, bar_pv + 16 * i, sl2, kv_valid,
-                                                 j, lane, tok_mine, tok_other, i == 0 || j + 1 < nkv, m_run, l_run, a, trole);
+        softmax_step<true, kEmu, kPing>(tS, tO, tP, bar_sfree + 8 * i, bar_p + 16 * i + 8 * half,
+                                        bar_pv + 16 * i + 8 * half, bar_pv + 16 * i + 8 * (half ^ 1), xr + 4 * half,
+                                        xr + 4 * (half ^ 1), pair_bar, 9 + i, 9 + (i ^ 1), i == 0 || j + 1 < nkv, sl2,
+                                        kv_valid, j, lane, m_run, l_run, a, trole);
     }
 
-    // epilogue: O_i / l -> bf16 -> global
-    mbar_wait(bar_pv + 16 * i + 8 * (kHalves - 1), (nkv - 1) & 1);  // the last commit covers the earlier one
+    // epilogue: row sum = both threads' shares; O_i / l -> bf16 -> global, 32 columns per thread
+    {
+      const uint32_t xr = xch_row + uint32_t((nkv & 1) * 2048);  // the parity the last block did not use
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(xr + 4 * half), "f"(l_run) : "memory");
+      pair_sync(pair_bar);  // also: the other half's warp has waited for its PV(nkv-2), so the parity waits below are unambiguous
+      float l_other;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(l_other) : "r"(xr + 4 * (half ^ 1)) : "memory");
+      l_run += l_other;
+    }
+    mbar_wait(bar_pv + 16 * i, (nkv - 1) & 1);
+    mbar_wait(bar_pv + 16 * i + 8, (nkv - 1) & 1);
     tc_fence_after();
     const int qrow = q0 + i * 128 + row;
     const float inv_l = 1.0f / l_run;
-    __nv_bfloat16* optr = a.o + (long long)b * a.bso + (long long)qrow * a.ldo + head * 64;
-    if (a.lse != nullptr && qrow < a.Lq)
+    if (a.lse != nullptr && half == 0 && qrow < a.Lq)
       a.lse[((long long)b * a.Hh + head) * a.Lq + qrow] = m_run + log2f(l_run);
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      tmem_ld32(tO + c * 32, v);
-      tmem_wait_ld();
-      if (a.lse != nullptr) {  // fp32 partial result
-        if (qrow < a.Lq) {
-          float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(a.o) + (long long)b * a.bso +
-                                                 (long long)qrow * a.ldo + head * 64 + c * 32);
+    uint32_t v[32];
+    tmem_ld32(tO, v);
+    tmem_wait_ld();
+    if (a.lse != nullptr) {  // fp32 partial result
+      if (qrow < a.Lq) {
+        float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(a.o) + (long long)b * a.bso +
+                                               (long long)qrow * a.ldo + head * 64 + half * 32);
 #pragma unroll
-          for (int q = 0; q < 8; ++q)
-            o4[q] = make_float4(__uint_as_float(v[4 * q]) * inv_l, __uint_as_float(v[4 * q + 1]) * inv_l,
-                                __uint_as_float(v[4 * q + 2]) * inv_l, __uint_as_float(v[4 * q + 3]) * inv_l);
-        }
-      } else if (qrow < a.Lq) {
-        uint4* o4 = reinterpret_cast<uint4*>(optr + c * 32);
+        for (int q = 0; q < 8; ++q)
+          o4[q] = make_float4(__uint_as_float(v[4 * q]) * inv_l, __uint_as_float(v[4 * q + 1]) * inv_l,
+                              __uint_as_float(v[4 * q + 2]) * inv_l, __uint_as_float(v[4 * q + 3]) * inv_l);
+      }
+    } else if (qrow < a.Lq) {
+      uint4* o4 = reinterpret_cast<uint4*>(a.o + (long long)b * a.bso + (long long)qrow * a.ldo + head * 64 + half * 32);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 u;
-          u.x = pack_bf16x2(__uint_as_float(v[q * 8 + 0]) * inv_l, __uint_as_float(v[q * 8 + 1]) * inv_l);
-          u.y = pack_bf16x2(__uint_as_float(v[q * 8 + 2]) * inv_l, __uint_as_float(v[q * 8 + 3]) * inv_l);
-          u.z = pack_bf16x2(__uint_as_float(v[q * 8 + 4]) * inv_l, __uint_as_float(v[q * 8 + 5]) * inv_l);
-          u.w = pack_bf16x2(__uint_as_float(v[q * 8 + 6]) * inv_l, __uint_as_float(v[q * 8 + 7]) * inv_l);
-          o4[q] = u;
-        }
+      for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(__uint_as_float(v[q * 8 + 0]) * inv_l, __uint_as_float(v[q * 8 + 1]) * inv_l);
+        u.y = pack_bf16x2(__uint_as_float(v[q * 8 + 2]) * inv_l, __uint_as_float(v[q * 8 + 3]) * inv_l);
+        u.z = pack_bf16x2(__uint_as_float(v[q * 8 + 4]) * inv_l, __uint_as_float(v[q * 8 + 5]) * inv_l);
+        u.w = pack_bf16x2(__uint_as_float(v[q * 8 + 6]) * inv_l, __uint_as_float(v[q * 8 + 7]) * inv_l);
+        o4[q] = u;
       }
     }
   }
@@ -605,36 +662,48 @@ static int attn_launch(const void* q, const void* k, const void* v, void* o, flo
   a.trace = trace_path ? trace_dev : nullptr;
 #endif
   dim3 grid((Lq + 255) / 256, Hh, B);
-#define SEVA_ATTN_LAUNCH(E, H, P)                                                                   \
+#define SEVA_ATTN_LAUNCH(E, P)                                                                      \
   {                                                                                                 \
-    if (ensure_dyn_smem(reinterpret_cast<const void*>(attn_kernel<E, H, P>), kAttnSmem)) return 2;  \
-    attn_kernel<E, H, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);              \
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(attn_kernel<E, P>), kAttnSmem)) return 2;     \
+    attn_kernel<E, P><<<grid, kAttnThreads, kAttnSmem, stream>>>(tmQ, tmK, tmV, a);                 \
   }
 #ifdef SEVA_DEBUG
-  // developer builds only: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_HALVES = 1, 2,
-  // SEVA_ATTN_PING = 0, 1
+  // developer builds only: SEVA_ATTN_EMU = 0, 2, 4, 6, 8 (n/16 of the exponentials on the FMA pipe), SEVA_ATTN_PING = 0 / 1
   static const int emu = [] { const char* e = getenv("SEVA_ATTN_EMU"); return e ? atoi(e) : kEmuDefault; }();
-  static const int halves = [] { const char* e = getenv("SEVA_ATTN_HALVES"); return e ? atoi(e) : kHalvesDefault; }();
   static const int ping = [] { const char* e = getenv("SEVA_ATTN_PING"); return e ? atoi(e) : (kPingDefault ? 1 : 0); }();
-#define SEVA_ATTN_EMU_SWITCH(H, P)                 \
-  switch (emu) {                                   \
-    case 0: SEVA_ATTN_LAUNCH(0, H, P) break;       \
-    case 2: SEVA_ATTN_LAUNCH(2, H, P) break;       \
-    case 6: SEVA_ATTN_LAUNCH(6, H, P) break;       \
-    case 8: SEVA_ATTN_LAUNCH(8, H, P) break;       \
-    default: SEVA_ATTN_LAUNCH(4, H, P) break;      \
+  if (ping) {
+    switch (emu) {
+      case 0: SEVA_ATTN_LAUNCH(0, true) break;
+      case 2: SEVA_ATTN_LAUNCH(2, true) break;
+      case 6: SEVA_ATTN_LAUNCH(6, true) break;
+      case 8: SEVA_ATTN_LAUNCH(8, true) break;
+      default: SEVA_ATTN_LAUNCH(4, true) break;
+    }
+  } else {
+    switch (emu) {
+      case 0: SEVA_ATTN_LAUNCH(0, false) break;
+      case 2: SEVA_ATTN_LAUNCH(2, false) break;
+      case 6: SEVA_ATTN_LAUNCH(6, false) break;
+      case 8: SEVA_ATTN_LAUNCH(8, false) break;
+      default: SEVA_ATTN_LAUNCH(4, false) break;
+    }
   }
-  if (halves == 2 && ping) SEVA_ATTN_EMU_SWITCH(2, true)
-  else if (halves == 2) SEVA_ATTN_EMU_SWITCH(2, false)
-  else if (ping) SEVA_ATTN_EMU_SWITCH(1, true)
-  else SEVA_ATTN_EMU_SWITCH(1, false)
-#undef SEVA_ATTN_EMU_SWITCH
 #else
-  SEVA_ATTN_LAUNCH(kEmuDefault, kHalvesDefault, kPingDefault)  // the one release instantiation
+  SEVA_ATTN_LAUNCH(kEmuDefault, kPingDefault)  // the one release instantiation
 #endif
 #undef SEVA_ATTN_LAUNCH
   SEVA_CUDA(cudaGetLastError());
 #if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
+  {
+    unsigned int rec[8];
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(rec, g_attn_timeout, sizeof(rec)) == cudaSuccess && rec[0] != 0) {
+      fprintf(stderr, "attn: mbarrier wait timed out at attn.cu:%u  barrier +%u (smem 0x%x) parity %u  block (%u,%u,%u) warp %u  mma j %u  producer seq %u\n",
+              rec[0], rec[1] - rec[5], rec[1], rec[2], rec[3] & 1023, (rec[3] >> 10) & 1023, rec[3] >> 20, rec[4], rec[6], rec[7]);
+      unsigned int zero[8] = {0};
+      cudaMemcpyToSymbol(g_attn_timeout, zero, sizeof(zero));
+    }
+  }
   if (a.trace) {
     static unsigned long long host[5 * 64 * 16];
     cudaDeviceSynchronize();
