@@ -229,6 +229,22 @@ int seva_softmax_rows(const float* x, int64_t ldx, void* y, int64_t ldy, int32_t
 /* fp32 rows -> bf16 rows (used for packing small inputs). */
 int seva_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 
+/* ---- CLIP conditioner / image preprocessing ------------------------------------- */
+/* kornia.geometry.resize(x, (OH, OW), interpolation="bicubic", align_corners=True, antialias=True) of
+ * CLIPConditioner.preprocess (seva/modules/conditioner.py:24-32) on `planes` fp32 planes of H x W: Gaussian blur with
+ * reflected borders (sigma = max((factor - 1) / 2, 0.001), int(max(4 sigma, 3)) taps made odd; only when downscaling) fused
+ * with torch's bicubic interpolation (A = -0.75, taps clamped to the image).  mean3 / std3 below are HOST pointers. */
+int seva_resize_bicubic_aa(const float* src, float* dst, int32_t planes, int32_t H, int32_t W, int32_t OH, int32_t OW,
+                           int32_t antialias, void* stream);
+/* (x + 1) / 2, per-channel (v - mean) / std (conditioner.py:33-35) and the im2col of open_clip's VisionTransformer.conv1
+ * (P x P, stride P, no bias): x fp32 [N, 3, S, S] -> bf16 rows [N * rows_per_img, ldo]; row 1 + patch index holds the patch as
+ * (c, ky, kx), row 0 (class-token slot), the rows after the last patch and the columns >= 3 P P are zero. */
+int seva_clip_patchify(const float* x, void* out, int32_t N, int32_t S, int32_t P, int32_t rows_per_img, int32_t ldo,
+                       const float* mean3, const float* std3, void* stream);
+/* F.interpolate(mode="area") (= adaptive average pooling) of load_img_and_K / transform_img_and_K
+ * (seva/eval.py:206-208, 289-291) on `planes` fp32 planes. */
+int seva_resize_area(const float* src, float* dst, int32_t planes, int32_t H, int32_t W, int32_t OH, int32_t OW, void* stream);
+
 /* ---- small dense ops ---------------------------------------------------------------------------- */
 /* out[n, 0:dim] = [cos(t[n]*f_k) | sin(t[n]*f_k)], f_k = exp(-ln(max_period)*k/(dim/2)); t int64. */
 int seva_timestep_embedding(const int64_t* t, float* out, int32_t N, int32_t dim, float max_period,

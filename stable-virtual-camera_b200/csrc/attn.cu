@@ -335,7 +335,9 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       // ring order = the order in which the MMA warp consumes and frees the tiles: K0, then per key block j
       // [K(j+1)], V(j)
       uint32_t s = 0, ph = 0;
+#if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
       uint32_t seq_dbg = 0;
+#endif
       auto load = [&](const CUtensorMap* tm, int j) {
 #if defined(SEVA_DEBUG) && defined(SEVA_ATTN_TRACE)
         if (lane == 0) asm volatile("st.shared.b32 [%0], %1;" ::"r"(smem_base + 516), "r"(seq_dbg++));

@@ -529,16 +529,17 @@ struct GNFinalizeArgs {
   float* gstats;          // [Nimg][groups][2]
 };
 
-constexpr int kFinLanes = 8;  // slot lanes per channel: lane j sums slots j, j + 8, ... in order; lanes are then added in order
+constexpr int kFinMaxLanes = 16;  // slot lanes per channel (= warps of the block): lane j sums slots j, j + L, ... in order
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(512)
 gn_finalize_kernel(const GNFinalizeArgs a) {
-  extern __shared__ double ch[];  // [kFinLanes][channels of this block][2]
+  extern __shared__ double ch[];  // [lanes][channels of this block][2]
   const int n = blockIdx.y;
   const int g0 = blockIdx.x * a.gpb;
   const int ng = min(a.gpb, a.groups - g0);
   const int c_begin = g0 * a.cpg, nch = ng * a.cpg;
-  const int lane_s = threadIdx.x / 32;       // slot lane (8 warps)
+  const int L = blockDim.x >> 5;             // slot lanes
+  const int lane_s = threadIdx.x >> 5;       // slot lane (one warp each)
   const int lane_c = threadIdx.x & 31;       // channel lane
   for (int cc = lane_c; cc < nch; cc += 32) {
     const int c = c_begin + cc;
@@ -551,15 +552,15 @@ gn_finalize_kernel(const GNFinalizeArgs a) {
     const float2* p = reinterpret_cast<const float2*>(a.part[src]) + ((long long)n * a.slots[src]) * Cs + cl;
     double s = 0.0, q = 0.0;
     int k = lane_s;
-    for (; k + 3 * kFinLanes < cnt; k += 4 * kFinLanes) {  // 4 independent loads in flight, added in slot order
-      const float2 v0 = __ldcg(p + (long long)k * Cs), v1 = __ldcg(p + (long long)(k + kFinLanes) * Cs);
-      const float2 v2 = __ldcg(p + (long long)(k + 2 * kFinLanes) * Cs), v3 = __ldcg(p + (long long)(k + 3 * kFinLanes) * Cs);
+    for (; k + 3 * L < cnt; k += 4 * L) {  // 4 independent loads in flight, added in slot order
+      const float2 v0 = __ldcg(p + (long long)k * Cs), v1 = __ldcg(p + (long long)(k + L) * Cs);
+      const float2 v2 = __ldcg(p + (long long)(k + 2 * L) * Cs), v3 = __ldcg(p + (long long)(k + 3 * L) * Cs);
       s += (double)v0.x; q += (double)v0.y;
       s += (double)v1.x; q += (double)v1.y;
       s += (double)v2.x; q += (double)v2.y;
       s += (double)v3.x; q += (double)v3.y;
     }
-    for (; k < cnt; k += kFinLanes) {
+    for (; k < cnt; k += L) {
       const float2 v = __ldcg(p + (long long)k * Cs);
       s += (double)v.x;
       q += (double)v.y;
@@ -568,17 +569,27 @@ gn_finalize_kernel(const GNFinalizeArgs a) {
     ch[2 * (lane_s * nch + cc) + 1] = q;
   }
   __syncthreads();
-  for (int g = threadIdx.x; g < ng; g += blockDim.x) {
+  // one warp per group: lane l adds entries l, l + 32, ... of the group's [lanes x channels] block in index order, then a
+  // fixed shuffle tree -- the order depends on the launch shape only, so the result is deterministic
+  for (int g = lane_s; g < ng; g += L) {
     double s = 0.0, q = 0.0;
-    for (int c = 0; c < a.cpg; ++c)
-      for (int j = 0; j < kFinLanes; ++j) {
-        s += ch[2 * (j * nch + g * a.cpg + c)];
-        q += ch[2 * (j * nch + g * a.cpg + c) + 1];
-      }
-    const double mean = s * a.inv_cnt;
-    const double var = fmax(q * a.inv_cnt - mean * mean, 0.0);
-    float2* dst = reinterpret_cast<float2*>(a.gstats) + (long long)n * a.groups + g0 + g;
-    *dst = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)a.eps)));
+    const int per = L * a.cpg;
+    for (int e = lane_c; e < per; e += 32) {
+      const int j = e / a.cpg, c = e - j * a.cpg;
+      s += ch[2 * (j * nch + g * a.cpg + c)];
+      q += ch[2 * (j * nch + g * a.cpg + c) + 1];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      s += __shfl_down_sync(0xffffffffu, s, off);
+      q += __shfl_down_sync(0xffffffffu, q, off);
+    }
+    if (lane_c == 0) {
+      const double mean = s * a.inv_cnt;
+      const double var = fmax(q * a.inv_cnt - mean * mean, 0.0);
+      float2* dst = reinterpret_cast<float2*>(a.gstats) + (long long)n * a.groups + g0 + g;
+      *dst = make_float2((float)mean, (float)(1.0 / sqrt(var + (double)a.eps)));
+    }
   }
 }
 
@@ -787,10 +798,15 @@ extern "C" int seva_groupnorm_finalize(const float* part0, int32_t C0, int32_t r
   a.inv_cnt = 1.0 / ((double)a.cpg * (double)pixels);
   a.eps = eps;
   a.gstats = gstats;
-  const size_t smem = sizeof(double) * 2 * kFinLanes * (size_t)gpb * a.cpg;
+  // slot lanes: enough warps that every lane has ~3 slots at most 4 loads deep (172 slots of a 72 x 72 image: 16 lanes)
+  const int max_slots = a.slots[0] > a.slots[1] ? a.slots[0] : a.slots[1];
+  int lanes = (max_slots + 7) / 8;
+  if (lanes < 4) lanes = 4;
+  if (lanes > kFinMaxLanes) lanes = kFinMaxLanes;
+  const size_t smem = sizeof(double) * 2 * lanes * (size_t)gpb * a.cpg;
   SEVA_CHECK(smem <= 40 * 1024, "seva_groupnorm_finalize: group of %d channels too wide", a.cpg);
   dim3 grid((groups + gpb - 1) / gpb, Nimg);
-  gn_finalize_kernel<<<grid, 256, smem, stream>>>(a);
+  gn_finalize_kernel<<<grid, 32 * lanes, smem, stream>>>(a);
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

@@ -501,3 +501,45 @@ def gemv_rows(x: torch.Tensor, W: torch.Tensor, bias: torch.Tensor | None, *, si
     check(_lib.load().seva_gemv_rows(x.data_ptr(), W.data_ptr(), _p(bias), out.data_ptr(), M, N, K, int(silu_in),
                                      int(silu_out), _stream()), "seva_gemv_rows")
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# CLIP conditioner / image preprocessing
+# ------------------------------------------------------------------------------------------------
+def resize_bicubic_aa(x: torch.Tensor, size: tuple[int, int], antialias: bool = True) -> torch.Tensor:
+    """kornia.geometry.resize(x, size, interpolation="bicubic", align_corners=True, antialias=...) on fp32 [..., H, W]."""
+    _req(x, torch.float32, "x")
+    x = x.contiguous()
+    H, W = x.shape[-2:]
+    out = torch.empty((*x.shape[:-2], size[0], size[1]), device=x.device, dtype=torch.float32)
+    check(_lib.load().seva_resize_bicubic_aa(x.data_ptr(), out.data_ptr(), x.numel() // (H * W), H, W, size[0], size[1],
+                                             int(antialias), _stream()), "seva_resize_bicubic_aa")
+    return out
+
+
+def resize_area(x: torch.Tensor, size: tuple[int, int]) -> torch.Tensor:
+    """F.interpolate(x, size, mode="area") on fp32 [..., H, W]."""
+    _req(x, torch.float32, "x")
+    x = x.contiguous()
+    H, W = x.shape[-2:]
+    out = torch.empty((*x.shape[:-2], size[0], size[1]), device=x.device, dtype=torch.float32)
+    check(_lib.load().seva_resize_area(x.data_ptr(), out.data_ptr(), x.numel() // (H * W), H, W, size[0], size[1],
+                                       _stream()), "seva_resize_area")
+    return out
+
+
+def clip_patchify(x: torch.Tensor, patch: int, rows_per_img: int, ldo: int, mean, std) -> torch.Tensor:
+    """x fp32 [N, 3, S, S] in [-1, 1] -> normalised bf16 patch rows [N * rows_per_img, ldo] (row 0 of every image = 0)."""
+    import ctypes
+
+    _req(x, torch.float32, "x")
+    x = x.contiguous()
+    N, C, S, S2 = x.shape
+    if C != 3 or S != S2:
+        raise _lib.SevaB200Error(f"clip_patchify: expected [N, 3, S, S], got {tuple(x.shape)}")
+    out = torch.empty((N * rows_per_img, ldo), device=x.device, dtype=torch.bfloat16)
+    m = (ctypes.c_float * 3)(*[float(v) for v in mean])
+    s = (ctypes.c_float * 3)(*[float(v) for v in std])
+    check(_lib.load().seva_clip_patchify(x.data_ptr(), out.data_ptr(), N, S, patch, rows_per_img, ldo, m, s, _stream()),
+          "seva_clip_patchify")
+    return out
