@@ -163,6 +163,21 @@ class Codec:
     embed: Callable | None = None
     dim: int = 1024
 
+    downsample: int = 1          # image pixels per latent pixel (8 for the VAE)
+    latent_channels: int | None = None
+
+    @classmethod
+    def from_modules(cls, ae, conditioner) -> "Codec":
+        """The modules ``do_sample`` calls either side of the path (eval.py:1245-1248, 1316): ``AutoEncoder.encode`` /
+        ``.decode`` (seva_b200.autoencoder, N3) and the ``CLIPConditioner`` (seva_b200.conditioner, N4).  The scene's
+        frame tables then hold RGB images in [-1, 1] and the sampler runs on their 8x smaller 4-channel latents."""
+        return cls(encode=ae.encode, decode=ae.decode, embed=conditioner, dim=conditioner.params.embed_dim,
+                   downsample=ae.downsample, latent_channels=4)
+
+    def latent_shape(self, frame_shape: tuple) -> tuple:
+        c, h, w = frame_shape
+        return (self.latent_channels or c, h // self.downsample, w // self.downsample)
+
     def tokens(self, imgs: torch.Tensor) -> torch.Tensor:
         if self.embed is not None:
             return self.embed(imgs)
@@ -240,7 +255,8 @@ def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Call
     sample_fn = sample_fn or sample_window
     M = scene.input_c2ws.shape[0]
     all_c2ws = scene.all_c2ws
-    lat_shape = tuple(scene.input_latents.shape[1:])
+    frame_shape = tuple(scene.input_latents.shape[1:])   # latents, or RGB frames with a VAE codec
+    lat_shape = codec.latent_shape(frame_shape)
     inputs = dict(img=scene.input_latents.cpu().float(), c2w=to_hom_pose(scene.input_c2ws.float()).cpu(),
                   K=scene.input_Ks.float().cpu())
     two_pass = len(plan.passes) == 2
@@ -254,7 +270,7 @@ def run_scene(scene: Scene, plan: ScenePlan, model, denoiser, make_sampler: Call
                             else scene.target_Ks[:1].repeat_interleave(scene.prior_c2ws.shape[0], 0)).float().cpu())
         else:
             table = dict(c2w=to_hom_pose(scene.target_c2ws.float()).cpu(), K=scene.target_Ks.float().cpu())
-        table["img"] = torch.zeros((table["c2w"].shape[0],) + lat_shape)
+        table["img"] = torch.zeros((table["c2w"].shape[0],) + frame_shape)
         # every rank draws the noise of every window, in window order (torch.randn per do_sample call, eval.py:1290)
         noise = [torch.randn((ps.T,) + lat_shape, generator=generator) for _ in ps.windows]
         if two_pass and last:

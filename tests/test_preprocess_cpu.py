@@ -79,5 +79,5 @@ def test_oracle_vit_shapes():
     x = torch.rand(2, 3, 40, 40, generator=torch.Generator().manual_seed(1)) * 2 - 1
     y = CO.conditioner_forward(sd, x, heads=2, size=28)
     assert y.shape == (2, 32) and torch.isfinite(y).all()
-    # key set of a tower: 12 tensors per block + 10 (conv1, class / positional embedding, ln_pre, ln_post, proj)
-    assert len(sd) == 2 * 12 + 10
+    # key set of a tower: 12 tensors per block + 8 (conv1, class / positional embedding, ln_pre, ln_post, proj)
+    assert len(sd) == 2 * 12 + 8

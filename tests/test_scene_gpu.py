@@ -138,3 +138,42 @@ def test_window_latents_do_not_depend_on_who_samples_them():
         SC._seed_step_noise("cuda", SC.window_noise_seed(7, 1, k))
         got = SC.sample_window(model, denoiser, sampler, win, rows, all_c2ws, x0, cfg, codec, 2.0, "cuda")
         assert torch.equal(got, want), k
+
+
+def test_scene_with_vae_and_clip_modules():
+    """N3 + N4 either side of the path: a one-pass scene on RGB frames through AutoEncoder.encode, the CLIP conditioner,
+    the sampler and AutoEncoder.decode (do_sample, eval.py:1245-1248, 1316) -- the whole per-window sequence on our kernels."""
+    from seva_b200.autoencoder import AutoEncoder
+    from seva_b200.conditioner import CLIPConditioner, ViTParams
+
+    T, H, steps, n_targets = 4, 128, 2, 5
+    prm = SevaParams(model_channels=64, num_frames=T)
+    with torch.device("meta"):
+        m = Seva(prm)
+    sd = synth.fill_state_dict({k: tuple(v.shape) for k, v in m.state_dict().items()}, seed=0)
+    m.load_state_dict(sd, assign=True)
+    model = SGMWrapper(m.eval()).to("cuda")
+    disc = S.DDPMDiscretization()
+    denoiser = S.DiscreteDenoiser(disc, num_idx=1000, device="cuda")
+    ae = AutoEncoder(chunk_size=None, seed=2).cuda()
+    clip = CLIPConditioner(ViTParams(image_size=56, patch_size=14, width=128, layers=2, heads=2, embed_dim=prm.context_dim),
+                           seed=3).cuda()
+    codec = SC.Codec.from_modules(ae, clip)
+    assert codec.latent_shape((3, H, H)) == (4, H // 8, H // 8)
+
+    def make_sampler(T_, wrap):
+        g = S.MultiviewCFG(1.2)
+        return S.EulerEDMSampler(disc, wrap(g) if wrap else g, num_steps=steps, s_churn=0.0, s_tmin=0.0, s_tmax=999.0,
+                                 s_noise=1.0, verbose=False, device="cuda")
+
+    g = torch.Generator().manual_seed(5)
+    traj, inp = PC.cameras(n_targets, 3), PC.cameras(1, 4)
+    opts = {"chunk_strategy": "nearest-gt", "cfg": 2.0}
+    frames = torch.rand(1, 3, H, H, generator=g) * 2 - 1
+    sc = SC.Scene(frames, inp, _K(1), traj, _K(n_targets), [0], list(range(1, n_targets + 1)))
+    plan = SC.plan_scene(sc, T, opts, task="img2trajvid", use_traj_prior=False)
+    out = SC.run_scene(sc, plan, model, denoiser, make_sampler, codec=codec, generator=torch.Generator().manual_seed(7))
+    assert out.shape == (n_targets, 3, H, H) and torch.isfinite(out).all()
+    # the same run again returns the same frames (per-window noise streams, no hidden state in the codec modules)
+    again = SC.run_scene(sc, plan, model, denoiser, make_sampler, codec=codec, generator=torch.Generator().manual_seed(7))
+    assert torch.equal(out, again)
