@@ -116,8 +116,10 @@ def main() -> int:
     # network restatement vs the reference modules on several small configurations (model.py:176-234)
     from oracle import synth
     worst_n = 0.0
-    for mc, T, h, w, heads_ch in ((32, 2, 8, 8, 32), (32, 3, 16, 24, 32), (64, 5, 24, 16, 64), (64, 4, 16, 16, 32)):
-        P = R.model.SevaParams(model_channels=mc, num_frames=T, num_head_channels=heads_ch)
+    for mc, T, h, w, heads_ch, depth in ((32, 2, 8, 8, 32, [1, 1, 1, 1]), (32, 3, 16, 24, 32, [1, 1, 1, 1]),
+                                         (64, 5, 24, 16, 64, [1, 1, 1, 1]), (64, 4, 16, 16, 32, [1, 1, 1, 1]),
+                                         (64, 3, 16, 16, 64, [2, 1, 3, 1])):
+        P = R.model.SevaParams(model_channels=mc, num_frames=T, num_head_channels=heads_ch, transformer_depth=depth)
         torch.manual_seed(mc + T)
         net = R.model.SGMWrapper(R.model.Seva(P).eval())
         sd = {k: v.detach().clone() for k, v in net.module.state_dict().items()}
@@ -130,7 +132,7 @@ def main() -> int:
             got = O.sgm_forward(sd, P, x, t, cc, num_frames=T)
         worst_n = max(worst_n, ((want - got).norm() / want.norm()).item())
     bad += worst_n > 1e-5
-    print(f"network forward (4 small configurations incl. non-square latents): max rel-L2 {worst_n:.2e}")
+    print(f"network forward (5 small configurations incl. non-square latents and transformer_depth 2 / 3): max rel-L2 {worst_n:.2e}")
     return int(bad > 0)
 
 

@@ -79,7 +79,7 @@ def resblock(sd, k, x, emb, dense):
 
 
 def multiview_transformer(sd, k, x, context, T, heads, unflatten, sp=None):
-    """transformer.py:215-247 with depth 1.  With ``sp`` (frame sequence-parallel restatement) ``x`` and
+    """transformer.py:215-247 (any transformer_depth: the state dict decides).  With ``sp`` (frame sequence-parallel restatement) ``x`` and
     ``context`` hold this rank's T frames of every batch element, ``sp.ctx0`` is ``context[::T_total]`` of the
     full batch and ``sp.gather(t, per_frame)`` concatenates dim 1 of ``t`` over the ranks (per_frame = keys per
     frame): only the 3D and the time-mix self-attention see other ranks' frames."""
@@ -94,24 +94,27 @@ def multiview_transformer(sd, k, x, context, T, heads, unflatten, sp=None):
     x = F.group_norm(x, 32, sd[k + ".norm.weight"], sd[k + ".norm.bias"], 1e-6)
     x = x.permute(0, 2, 3, 1).reshape(n, h * w, c)
     x = _lin(sd, k + ".proj_in", x)
-    tb, tm = k + ".transformer_blocks.0", k + ".time_mix_blocks.0"
-    if unflatten:
-        x = x.reshape(n // T, T * h * w, c)
-    # TransformerBlock.forward (:106-110)
-    x = _attention(sd, tb + ".attn1", _ln(sd, tb + ".norm1", x), None, heads, g3 if unflatten else None) + x
-    x = _attention(sd, tb + ".attn2", _ln(sd, tb + ".norm2", x), context, heads) + x
-    x = _ff(sd, tb + ".ff", _ln(sd, tb + ".norm3", x)) + x
-    if unflatten:
-        x = x.reshape(n, h * w, c)
-    # TransformerBlockTimeMix.forward (:145-155)
-    s = h * w
-    y = x.reshape(n // T, T, s, c).transpose(1, 2).reshape(-1, T, c)
-    y = _ff(sd, tm + ".ff_in", _ln(sd, tm + ".norm_in", y)) + y
-    y = _attention(sd, tm + ".attn1", _ln(sd, tm + ".norm1", y), None, heads, gt) + y
-    y = _attention(sd, tm + ".attn2", _ln(sd, tm + ".norm2", y), time_ctx, heads) + y
-    y = _ff(sd, tm + ".ff", _ln(sd, tm + ".norm3", y))
-    y = y.reshape(n // T, s, T, c).transpose(1, 2).reshape(n, s, c)
-    x = x + y  # SkipConnect (:158-165)
+    d = 0
+    while f"{k}.transformer_blocks.{d}.norm1.weight" in sd:   # transformer_depth pairs (:234-241)
+        tb, tm = f"{k}.transformer_blocks.{d}", f"{k}.time_mix_blocks.{d}"
+        if unflatten:
+            x = x.reshape(n // T, T * h * w, c)
+        # TransformerBlock.forward (:106-110)
+        x = _attention(sd, tb + ".attn1", _ln(sd, tb + ".norm1", x), None, heads, g3 if unflatten else None) + x
+        x = _attention(sd, tb + ".attn2", _ln(sd, tb + ".norm2", x), context, heads) + x
+        x = _ff(sd, tb + ".ff", _ln(sd, tb + ".norm3", x)) + x
+        if unflatten:
+            x = x.reshape(n, h * w, c)
+        # TransformerBlockTimeMix.forward (:145-155)
+        s = h * w
+        y = x.reshape(n // T, T, s, c).transpose(1, 2).reshape(-1, T, c)
+        y = _ff(sd, tm + ".ff_in", _ln(sd, tm + ".norm_in", y)) + y
+        y = _attention(sd, tm + ".attn1", _ln(sd, tm + ".norm1", y), None, heads, gt) + y
+        y = _attention(sd, tm + ".attn2", _ln(sd, tm + ".norm2", y), time_ctx, heads) + y
+        y = _ff(sd, tm + ".ff", _ln(sd, tm + ".norm3", y))
+        y = y.reshape(n // T, s, T, c).transpose(1, 2).reshape(n, s, c)
+        x = x + y  # SkipConnect (:158-165)
+        d += 1
     x = _lin(sd, k + ".proj_out", x)
     return x.reshape(n, h, w, c).permute(0, 3, 1, 2) + x_in
 

@@ -119,23 +119,24 @@ def pack_weights(model: Seva) -> dict:
                     d["bs"] = _f32(m.skip_connection.bias)
                 P[id(m)] = d
             elif isinstance(m, MultiviewTransformer):
-                assert len(m.transformer_blocks) == 1, "transformer depth > 1 is not wired into the plan yet"
-                tb, tm = m.transformer_blocks[0], m.time_mix_blocks[0]
                 fold = _can_fold(m.in_channels)
+                pairs = []
+                for tb, tm in zip(m.transformer_blocks, m.time_mix_blocks):   # transformer_depth pairs (transformer.py:234)
+                    pairs.append(dict(
+                        s_attn1=_pack_attn_self_ln(tb.attn1, tb.norm1) if fold else _pack_attn_self(tb.attn1),
+                        s_attn2=_pack_attn_cross(tb.attn2),
+                        s_ff=_pack_ff_ln(tb.ff, tb.norm3) if fold else _pack_ff(tb.ff, dev),
+                        s_n1=_pack_ln(tb.norm1), s_n2=_pack_ln(tb.norm2), s_n3=_pack_ln(tb.norm3),
+                        t_nin=_pack_ln(tm.norm_in),
+                        t_ffin=_pack_ff_ln(tm.ff_in, tm.norm_in) if fold else _pack_ff(tm.ff_in, dev),
+                        t_attn1=_pack_attn_self_ln(tm.attn1, tm.norm1) if fold else _pack_attn_self(tm.attn1),
+                        t_attn2=_pack_attn_cross(tm.attn2),
+                        t_ff=_pack_ff_ln(tm.ff, tm.norm3) if fold else _pack_ff(tm.ff, dev),
+                        t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3)))
                 P[id(m)] = dict(
                     gn=dict(g=_f32(m.norm.weight), b=_f32(m.norm.bias), eps=float(m.norm.eps)),
                     win=pack.pack_linear(m.proj_in.weight), bin=_f32(m.proj_in.bias),
-                    wout=pack.pack_linear(m.proj_out.weight), bout=_f32(m.proj_out.bias),
-                    s_attn1=_pack_attn_self_ln(tb.attn1, tb.norm1) if fold else _pack_attn_self(tb.attn1),
-                    s_attn2=_pack_attn_cross(tb.attn2),
-                    s_ff=_pack_ff_ln(tb.ff, tb.norm3) if fold else _pack_ff(tb.ff, dev),
-                    s_n1=_pack_ln(tb.norm1), s_n2=_pack_ln(tb.norm2), s_n3=_pack_ln(tb.norm3),
-                    t_nin=_pack_ln(tm.norm_in),
-                    t_ffin=_pack_ff_ln(tm.ff_in, tm.norm_in) if fold else _pack_ff(tm.ff_in, dev),
-                    t_attn1=_pack_attn_self_ln(tm.attn1, tm.norm1) if fold else _pack_attn_self(tm.attn1),
-                    t_attn2=_pack_attn_cross(tm.attn2),
-                    t_ff=_pack_ff_ln(tm.ff, tm.norm3) if fold else _pack_ff(tm.ff, dev),
-                    t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3), ln_fold=fold)
+                    wout=pack.pack_linear(m.proj_out.weight), bout=_f32(m.proj_out.bias), pairs=pairs, ln_fold=fold)
             elif isinstance(m, Downsample):
                 P[id(m)] = dict(w=pack.pack_conv3x3(m.op.weight), b=_f32(m.op.bias))
             elif isinstance(m, Upsample):
@@ -831,108 +832,112 @@ class Engine:
         rows = self._rows(l, C_) if fold else None
         self.gemm(xn, w["win"], x0, bias=w["bin"], ln_rows=rows)
 
-        # ---- spatial block (TransformerBlock.forward, transformer.py:106-110)
-        a = self.buf(f"tk_ln_{l}", rc, C_)
-        if not fold:
-            self.ln(x0, w["s_n1"], a)
-        qkv_in = dict(A=x0, ln=dict(ln_in=rows, ln_eps=w["s_attn1"]["eps"])) if fold else dict(A=a, ln={})
-        qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
-        o = self.buf(f"tk_o_{l}", rc, C_)
-        bat, Lseq = (B, T * S) if is3d else (self.N, S)
-        sh = self.shard
-        if is3d and sh is not None:
-            # frame sequence-parallel 3D attention: local queries against the keys / values of all Tk frames
-            ring = os.environ.get("SEVA_RING", "ring")   # ring | allgather (both overlapped) | off (blocking gather)
-            Lk = self.Tk * S
-            if ring != "off":
-                box = {}
+        # transformer_depth (block, mix_block) pairs (transformer.py:234-241); the buffers are reused pair after pair
+        for d, pw in enumerate(w["pairs"]):
+            more = d + 1 < len(w["pairs"])
+            # ---- spatial block (TransformerBlock.forward, transformer.py:106-110)
+            a = self.buf(f"tk_ln_{l}", rc, C_)
+            if not fold:
+                self.ln(x0, pw["s_n1"], a)
+            qkv_in = dict(A=x0, ln=dict(ln_in=rows, ln_eps=pw["s_attn1"]["eps"])) if fold else dict(A=a, ln={})
+            qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
+            o = self.buf(f"tk_o_{l}", rc, C_)
+            bat, Lseq = (B, T * S) if is3d else (self.N, S)
+            sh = self.shard
+            if is3d and sh is not None:
+                # frame sequence-parallel 3D attention: local queries against the keys / values of all Tk frames
+                ring = os.environ.get("SEVA_RING", "ring")   # ring | allgather (both overlapped) | off (blocking gather)
+                Lk = self.Tk * S
+                if ring != "off":
+                    box = {}
 
-                def after_kv(q_, kvl_):
-                    box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, C_, mode=ring)
-                    self.add(_RingStart(box["ring"]), tag="start")
+                    def after_kv(q_, kvl_):
+                        box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, C_, mode=ring)
+                        self.add(_RingStart(box["ring"]), tag="start")
 
-                q, kvl, _ = self._split_qkv(qkv_in, w["s_attn1"], l, C_, S, gather=False, after_kv=after_kv)
-                self.add(box["ring"],
-                         flops=4.0 * bat * heads * Lseq * Lk * 64, nbytes=2.0 * bat * Lk * 2 * C_,
-                         tag=f"attn3d+exchange B{bat} H{heads} Lq{Lseq} Lk{Lk} {ring}")
-                self._touch_forward(q, o)
+                    q, kvl, _ = self._split_qkv(qkv_in, pw["s_attn1"], l, C_, S, gather=False, after_kv=after_kv)
+                    self.add(box["ring"],
+                             flops=4.0 * bat * heads * Lseq * Lk * 64, nbytes=2.0 * bat * Lk * 2 * C_,
+                             tag=f"attn3d+exchange B{bat} H{heads} Lq{Lseq} Lk{Lk} {ring}")
+                    self._touch_forward(q, o)
+                else:
+                    q, kvl, kvf = self._split_qkv(qkv_in, pw["s_attn1"], l, C_, S)
+                    self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
+                             heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
+                             Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
+                             tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
+                    self._touch_forward(q, kvf, o)
             else:
-                q, kvl, kvf = self._split_qkv(qkv_in, w["s_attn1"], l, C_, S)
-                self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
-                         heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
-                         Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
-                         tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
-                self._touch_forward(q, kvf, o)
-        else:
-            self._qkv(qkv_in, w["s_attn1"], slice(None), qkv)
-            ld = qkv.stride(0)
-            base = qkv.data_ptr()
-            self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
-                     ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
-                     flops=4.0 * bat * heads * Lseq * Lseq * 64,
-                     tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
-            self._touch_forward(qkv, o)
-        x1 = self.buf(f"tk_x1_{l}", rc, C_)
-        if self.L == 1:
-            xr = self._cross_vec(w["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}")
-            self.gemm(o, w["s_attn1"]["wo"], x1, bias=w["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq,
-                      ln_rows=rows)
-        else:
-            x1a = self.buf(f"tk_x1a_{l}", rc, C_)
-            self.gemm(o, w["s_attn1"]["wo"], x1a, bias=w["s_attn1"]["bo"], residual=x0)
-            self._cross_general(w["s_attn2"], w["s_n2"], x1a, x1, l, C_, heads, bat, Lseq,
-                                self.ctx0_in if is3d else self.ctx_in, out_rows=rows)
-        x2 = self.buf(f"tk_x2_{l}", rc, C_)
-        self._ff(x1, w["s_n3"], w["s_ff"], x1, x2, l, C_, "s", x_rows=rows, out_rows=rows)
+                self._qkv(qkv_in, pw["s_attn1"], slice(None), qkv)
+                ld = qkv.stride(0)
+                base = qkv.data_ptr()
+                self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
+                         ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
+                         flops=4.0 * bat * heads * Lseq * Lseq * 64,
+                         tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
+                self._touch_forward(qkv, o)
+            x1 = self.buf(f"tk_x1_{l}", rc, C_)
+            if self.L == 1:
+                xr = self._cross_vec(pw["s_attn2"], ctx0 if is3d else ctx2, C_, f"s{id(m)}_{d}")
+                self.gemm(o, pw["s_attn1"]["wo"], x1, bias=pw["s_attn1"]["bo"], residual=x0, rowbias=xr, rowbias_rpi=Lseq,
+                          ln_rows=rows)
+            else:
+                x1a = self.buf(f"tk_x1a_{l}", rc, C_)
+                self.gemm(o, pw["s_attn1"]["wo"], x1a, bias=pw["s_attn1"]["bo"], residual=x0)
+                self._cross_general(pw["s_attn2"], pw["s_n2"], x1a, x1, l, C_, heads, bat, Lseq,
+                                    self.ctx0_in if is3d else self.ctx_in, out_rows=rows)
+            x2 = self.buf(f"tk_x2_{l}", rc, C_)
+            self._ff(x1, pw["s_n3"], pw["s_ff"], x1, x2, l, C_, "s", x_rows=rows, out_rows=rows)
 
-        # ---- time-mix block (TransformerBlockTimeMix.forward, transformer.py:145-155), tokens stay (b t) s
-        y1 = self.buf(f"tk_y1_{l}", rc, C_)
-        self._ff(x2, w["t_nin"], w["t_ffin"], x2, y1, l, C_, "tin", x_rows=rows, out_rows=rows)
-        if not fold:
-            self.ln(y1, w["t_n1"], a)
-        qkv_in = dict(A=y1, ln=dict(ln_in=rows, ln_eps=w["t_attn1"]["eps"])) if fold else dict(A=a, ln={})
-        if sh is not None and self.tm_a2a and S >= sh.size:
-            sa, sb = sh.space_parts(S)[sh.rank]
-            S_me = sb - sa
-            self._qkv(qkv_in, w["t_attn1"], slice(None), qkv)
-            qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * C_)
-            o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, C_)
-            self.add(_SpaceExchange(sh, True, qkv, qkv_sp, B, S), nbytes=2.0 * (qkv.numel() + qkv_sp.numel()),
-                     tag=f"to_space rows{rc} C{3 * C_}")
-            self.add(self.lib.seva_timemix_attn, qkv_sp.data_ptr(), o_sp.data_ptr(), B, self.Tk, S_me, heads,
-                     qkv_sp.stride(0), o_sp.stride(0), 0.125, flops=4.0 * B * S_me * heads * self.Tk * self.Tk * 64,
-                     nbytes=2.0 * 4 * qkv_sp.shape[0] * C_, tag=f"timemix BS{B * S_me} H{heads} T{self.Tk}")
-            self.add(_SpaceExchange(sh, False, o_sp, o, B, S), nbytes=2.0 * (o_sp.numel() + o.numel()),
-                     tag=f"to_frames rows{rc} C{C_}")
-            self._touch_forward(qkv, o)
-        elif sh is not None:
-            q, kvl, kvf = self._split_qkv(qkv_in, w["t_attn1"], l, C_, S)
-            self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
-                     o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
-                     flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
-                     tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
-            self._touch_forward(q, kvf, o)
-        else:
-            self._qkv(qkv_in, w["t_attn1"], slice(None), qkv)
-            self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
-                     o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
-                     tag=f"timemix BS{B * S} H{heads}")
-            self._touch_forward(qkv, o)
-        y2 = self.buf(f"tk_y2_{l}", rc, C_)
-        if self.L == 1:
-            xr = self._cross_vec(w["t_attn2"], ctx0, C_, f"t{id(m)}")
-            self.gemm(o, w["t_attn1"]["wo"], y2, bias=w["t_attn1"]["bo"], residual=y1, rowbias=xr,
-                      rowbias_rpi=T * S, ln_rows=rows)
-        else:
-            # time_context = context[::T] repeated over the positions (transformer.py:222-226): every token of batch
-            # element b attends to the same L context tokens, and cross-attention is per query token, so the (b t) s
-            # token order needs no transpose: batch = B, T * S queries each
-            y2a = self.buf(f"tk_x1a_{l}", rc, C_)
-            self.gemm(o, w["t_attn1"]["wo"], y2a, bias=w["t_attn1"]["bo"], residual=y1)
-            self._cross_general(w["t_attn2"], w["t_n2"], y2a, y2, l, C_, heads, B, T * S, self.ctx0_in, out_rows=rows)
-        x3 = self.buf(f"tk_x3_{l}", rc, C_)
-        # x = x_spatial + ff(norm3(y2)): SkipConnect (transformer.py:158-165) folded into the residual
-        self._ff(y2, w["t_n3"], w["t_ff"], x2, x3, l, C_, "t", x_rows=rows)
+            # ---- time-mix block (TransformerBlockTimeMix.forward, transformer.py:145-155), tokens stay (b t) s
+            y1 = self.buf(f"tk_y1_{l}", rc, C_)
+            self._ff(x2, pw["t_nin"], pw["t_ffin"], x2, y1, l, C_, "tin", x_rows=rows, out_rows=rows)
+            if not fold:
+                self.ln(y1, pw["t_n1"], a)
+            qkv_in = dict(A=y1, ln=dict(ln_in=rows, ln_eps=pw["t_attn1"]["eps"])) if fold else dict(A=a, ln={})
+            if sh is not None and self.tm_a2a and S >= sh.size:
+                sa, sb = sh.space_parts(S)[sh.rank]
+                S_me = sb - sa
+                self._qkv(qkv_in, pw["t_attn1"], slice(None), qkv)
+                qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * C_)
+                o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, C_)
+                self.add(_SpaceExchange(sh, True, qkv, qkv_sp, B, S), nbytes=2.0 * (qkv.numel() + qkv_sp.numel()),
+                         tag=f"to_space rows{rc} C{3 * C_}")
+                self.add(self.lib.seva_timemix_attn, qkv_sp.data_ptr(), o_sp.data_ptr(), B, self.Tk, S_me, heads,
+                         qkv_sp.stride(0), o_sp.stride(0), 0.125, flops=4.0 * B * S_me * heads * self.Tk * self.Tk * 64,
+                         nbytes=2.0 * 4 * qkv_sp.shape[0] * C_, tag=f"timemix BS{B * S_me} H{heads} T{self.Tk}")
+                self.add(_SpaceExchange(sh, False, o_sp, o, B, S), nbytes=2.0 * (o_sp.numel() + o.numel()),
+                         tag=f"to_frames rows{rc} C{C_}")
+                self._touch_forward(qkv, o)
+            elif sh is not None:
+                q, kvl, kvf = self._split_qkv(qkv_in, pw["t_attn1"], l, C_, S)
+                self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
+                         o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
+                         flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
+                         tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
+                self._touch_forward(q, kvf, o)
+            else:
+                self._qkv(qkv_in, pw["t_attn1"], slice(None), qkv)
+                self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
+                         o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
+                         tag=f"timemix BS{B * S} H{heads}")
+                self._touch_forward(qkv, o)
+            y2 = self.buf(f"tk_y2_{l}", rc, C_)
+            if self.L == 1:
+                xr = self._cross_vec(pw["t_attn2"], ctx0, C_, f"t{id(m)}_{d}")
+                self.gemm(o, pw["t_attn1"]["wo"], y2, bias=pw["t_attn1"]["bo"], residual=y1, rowbias=xr,
+                          rowbias_rpi=T * S, ln_rows=rows)
+            else:
+                # time_context = context[::T] repeated over the positions (transformer.py:222-226): every token of batch
+                # element b attends to the same L context tokens, and cross-attention is per query token, so the (b t) s
+                # token order needs no transpose: batch = B, T * S queries each
+                y2a = self.buf(f"tk_x1a_{l}", rc, C_)
+                self.gemm(o, pw["t_attn1"]["wo"], y2a, bias=pw["t_attn1"]["bo"], residual=y1)
+                self._cross_general(pw["t_attn2"], pw["t_n2"], y2a, y2, l, C_, heads, B, T * S, self.ctx0_in, out_rows=rows)
+            x3 = self.buf(f"tk_x3_{l}", rc, C_)
+            # x = x_spatial + ff(norm3(y2)): SkipConnect (transformer.py:158-165) folded into the residual
+            self._ff(y2, pw["t_n3"], pw["t_ff"], x2, x3, l, C_, "t", x_rows=rows, out_rows=rows if more else None)
+            x0 = x3   # input of the next (block, mix_block) pair
         # proj_out + input residual, written back to the zero-bordered layout (transformer.py:244-247); its epilogue
         # also leaves the GroupNorm partials of the block output for the next ResBlock
         self.gemm(x3, w["wout"], out, bias=w["bout"], residual=x, out_map=1, H=H, Wd=Wd, gn_rpi=S)
