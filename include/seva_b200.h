@@ -52,8 +52,10 @@ typedef struct SevaGemm {
   const void* W;       /* bf16 [N, ntaps*Kc] row-major (K-major), row stride ldw elements              */
   int64_t ldw;
   int32_t M, N, Kc;    /* output rows, output columns (before GEGLU halving), reduction per tap        */
-  int32_t ntaps;       /* 1 = plain GEMM, 9 = 3x3 conv over a zero-bordered flat image                 */
-  int32_t tap_wp;      /* padded image width Wp: tap t reads row m + (t/3-1)*Wp + (t%3-1)              */
+  int32_t ntaps;       /* 1 = plain GEMM, 9 = 3x3 conv over a zero-bordered flat image, 4 = one output phase of
+                        * Upsample.forward (nearest 2x + 3x3 conv, seva/modules/layers.py:42-46), see out_map    */
+  int32_t tap_wp;      /* padded image width Wp: tap t reads row m + (t/3-1)*Wp + (t%3-1)  (ntaps = 9);
+                        * ntaps = 4: row m + (t/2 + py - 1)*Wp + (t%2 + px - 1)                                  */
   const float* bias;   /* fp32 [N] or NULL                                                              */
   const float* rowbias;/* fp32 [ceil(M/rowbias_rpi), Nout] or NULL; added to every row of a row group   */
   int32_t rowbias_rpi;
@@ -65,6 +67,11 @@ typedef struct SevaGemm {
   int32_t geglu;       /* 1: W rows are tile-interleaved [x | gate]; out[:, j] = x_j * gelu(gate_j)     */
   int32_t out_map;     /* 0: row m -> m.  1: compact (n, y, x) of an HxW image -> zero-bordered flat    */
   int32_t H, Wd;       /*    row n*(H+2)*(Wd+2) + (y+1)*(Wd+2) + x+1                                     */
+                       /* 2 + 2*py + px (with ntaps = 4): A is the zero-bordered H x Wd image; interior pixel (Y, X) of
+                        *    row m is written to pixel (2Y-1+py, 2X-1+px) of the zero-bordered 2H x 2Wd image.  Nearest-2x
+                        *    upsampling followed by a 3x3 conv is, per output phase (py, px), a 2x2 conv on the SOURCE
+                        *    image whose taps are sums of the 3x3 taps (16/36 of the multiply-adds, no upsampled copy);
+                        *    W holds that phase's [N, 4*Kc] taps.  The four launches leave the output border untouched. */
   int32_t mask_border; /* 1: rows are zero-bordered flat (Hp x Wp per image): border rows written as 0 */
   int32_t Hp, Wp;
   int32_t bn;          /* N tile (multiple of 32, <= 256; GEGLU: multiple of 64); 0 = choose            */

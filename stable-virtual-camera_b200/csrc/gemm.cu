@@ -472,6 +472,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int tap = 0; tap < a.ntaps; ++tap) {
           int off = 0;
           if (a.ntaps == 9) off = (tap / 3 - 1) * a.tap_wp + (tap % 3 - 1);
+          // 2 x 2 taps of one output phase of nearest-2x upsampling + 3 x 3 conv (out_map = 2 + 2 * py + px)
+          else if (a.ntaps == 4) off = ((tap >> 1) + ((a.out_map - 2) >> 1) - 1) * a.tap_wp + ((tap & 1) + ((a.out_map - 2) & 1) - 1);
           for (int kc = 0; kc < a.kchunks; ++kc, ++it_g) {
             mbar_wait(bar_empty + 8 * s, ph ^ 1);
             const uint32_t sa = ring_base + s * stage_bytes;
@@ -701,6 +703,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const int y = r / a.Wd;
           const int x = r - y * a.Wd;
           ri.out_row = (long long)img * (a.H + 2) * (a.Wd + 2) + (long long)(y + 1) * (a.Wd + 2) + x + 1;
+        }
+        if (a.out_map >= 2) {
+          // row m = pixel (Y, X) of the zero-bordered LOW-resolution image -> pixel (2Y - 1 + py, 2X - 1 + px) of the
+          // zero-bordered image of twice the size; the low-resolution border rows produce nothing
+          const int hwp = (a.H + 2) * (a.Wd + 2);
+          const int img = m / hwp;
+          const int r = m - img * hwp;
+          const int Y = r / (a.Wd + 2);
+          const int X = r - Y * (a.Wd + 2);
+          const int py = (a.out_map - 2) >> 1, px = (a.out_map - 2) & 1;
+          ri.valid = Y >= 1 && Y <= a.H && X >= 1 && X <= a.Wd;
+          ri.out_row = (long long)img * (2 * a.H + 2) * (2 * a.Wd + 2) + (long long)(2 * Y - 1 + py) * (2 * a.Wd + 2) +
+                       2 * X - 1 + px;
         }
         if (a.mask_border) {
           const int r = m % (a.Hp * a.Wp);
@@ -947,8 +962,14 @@ extern "C" int seva_gemm_bf16(const SevaGemm* g, void* stream_v) {
   SEVA_CHECK(g->A && g->W && g->out, "seva_gemm_bf16: null A/W/out");
   SEVA_CHECK(g->M > 0 && g->N > 0 && g->Kc > 0, "seva_gemm_bf16: bad sizes M=%d N=%d Kc=%d", g->M,
              g->N, g->Kc);
-  SEVA_CHECK(g->ntaps == 1 || g->ntaps == 9, "seva_gemm_bf16: ntaps must be 1 or 9 (got %d)",
+  SEVA_CHECK(g->ntaps == 1 || g->ntaps == 9 || g->ntaps == 4, "seva_gemm_bf16: ntaps must be 1, 4 or 9 (got %d)",
              g->ntaps);
+  SEVA_CHECK(g->out_map >= 0 && g->out_map <= 5 && (g->ntaps == 4) == (g->out_map >= 2),
+             "seva_gemm_bf16: ntaps = 4 goes with out_map = 2..5 (upsampling phase) and nothing else");
+  SEVA_CHECK(g->out_map < 2 || (g->H > 0 && g->Wd > 0 && g->tap_wp == g->Wd + 2 && g->residual == nullptr &&
+                                g->gn_partial == nullptr && g->ln_rowstats == nullptr && !g->mask_border && !g->geglu &&
+                                !g->out_fp32),
+             "seva_gemm_bf16: upsampling phase needs H, Wd, tap_wp = Wd + 2 and a plain bf16 epilogue");
   SEVA_CHECK((g->lda % 8) == 0 && (g->ldw % 8) == 0 && (g->Kc % 8) == 0,
              "seva_gemm_bf16: lda/ldw/Kc must be multiples of 8 (16-byte TMA strides)");
   SEVA_CHECK((reinterpret_cast<uintptr_t>(g->A) & 15) == 0 &&

@@ -176,7 +176,7 @@ def pack_weights(m: AutoencoderKL) -> dict:
         us = None
         if hasattr(blk, "upsamplers"):
             cv = blk.upsamplers[0].conv
-            us = (pack.pack_conv3x3(cv.weight), _f32(cv.bias))
+            us = (pack.pack_upconv_phases(cv.weight), _f32(cv.bias))
         P["d_up"].append(([_pack_resnet(r) for r in blk.resnets], us))
     P["d_no_g"], P["d_no_b"] = _f32(d.conv_norm_out.weight), _f32(d.conv_norm_out.bias)
     w3 = torch.zeros(4, *d.conv_out.weight.shape[1:], device=dev)      # 3 -> 4 output channels (fp32 rows of 16 bytes)
@@ -260,11 +260,16 @@ class _Run:
         ops.run_gemm(g)
         return out
 
-    def up(self, x, H, W, w9, b):
+    def up(self, x, H, W, wph, b):
+        """Upsample2D: conv3x3(nearest2x(x)) as four 2x2-tap phase convolutions on x itself (SevaGemm.out_map = 2..5)."""
         c = x.shape[1]
-        big = torch.empty((self.rows(2 * H, 2 * W), c), device=self.dev, dtype=BF16)
-        ops.upsample2x_pad(x, big, self.n, H, W, c)
-        return self.conv(big, 2 * H, 2 * W, w9, b)
+        out = torch.zeros((self.rows(2 * H, 2 * W), wph[0].shape[0]), device=self.dev, dtype=BF16)
+        for ph in range(4):
+            g = ops.make_gemm(A_ptr=x.data_ptr(), lda=x.stride(0), a_rows=x.shape[0], W_ptr=wph[ph].data_ptr(),
+                              ldw=wph[ph].stride(0), M=x.shape[0], N=wph[ph].shape[0], Kc=c, out_ptr=out.data_ptr(),
+                              ldo=out.stride(0), ntaps=4, tap_wp=W + 2, bias_ptr=b.data_ptr(), out_map=2 + ph, H=H, Wd=W)
+            ops.run_gemm(g)
+        return out
 
 
 def _encode_cuda(P: dict, x: torch.Tensor) -> torch.Tensor:

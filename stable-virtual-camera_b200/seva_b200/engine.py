@@ -140,7 +140,7 @@ def pack_weights(model: Seva) -> dict:
             elif isinstance(m, Downsample):
                 P[id(m)] = dict(w=pack.pack_conv3x3(m.op.weight), b=_f32(m.op.bias))
             elif isinstance(m, Upsample):
-                P[id(m)] = dict(w=pack.pack_conv3x3(m.conv.weight), b=_f32(m.conv.bias))
+                P[id(m)] = dict(wph=pack.pack_upconv_phases(m.conv.weight), b=_f32(m.conv.bias))
     return P
 
 
@@ -536,7 +536,8 @@ class Engine:
         m_alg = M if alg_rows is None else alg_rows
         kk = (A.shape[1] if Kc is None else Kc) if alg_k is None else alg_k
         self.add(self.lib.seva_gemm_bf16, C.byref(g), flops=2.0 * m_alg * W.shape[0] * kk * ntaps,
-                 tag=("conv3x3" if ntaps == 9 else ("geglu" if geglu else "linear")) + f" M{M} N{W.shape[0]} K{kk * ntaps}")
+                 tag=("conv3x3" if ntaps == 9 else ("upconv" if ntaps == 4 else ("geglu" if geglu else "linear")))
+                 + f" M{M} N{W.shape[0]} K{int(kk * ntaps)}")
 
     def conv3x3(self, x, l, W9, bias, out, *, rowbias=None, residual=None, out_fp32=False, alg_k=None, stats=True):
         H, Wd = self.HW[l]
@@ -771,14 +772,15 @@ class Engine:
 
     # Upsample.forward, layers.py:42-46
     def _up(self, m: Upsample, x, l, out):
+        """Nearest-2x upsampling + 3x3 conv as four 2x2-tap phase convolutions on the SOURCE image (SevaGemm.out_map = 2..5):
+        16/36 of the multiply-adds of the upsample-then-convolve form and no upsampled copy.  ``out`` keeps the zero
+        border it was allocated with (no launch of the plan writes non-zero border rows)."""
         w = self.P[id(m)]
         H, Wd = self.HW[l]
-        up = self.buf(f"up_{l - 1}", self.rows_p(l - 1), m.channels)
-        self.add(self.lib.seva_upsample2x_pad, x.data_ptr(), x.stride(0), up.data_ptr(), up.stride(0), self.N, H,
-                 Wd, m.channels)
-        self._touch_forward(x, up)
-        self.keep += [x]
-        self.conv3x3(up, l - 1, w["w"], w["b"], out)
+        cin = m.channels
+        for ph in range(4):
+            self.gemm(x, w["wph"][ph], out, bias=w["b"], ntaps=4, tap_wp=Wd + 2, out_map=2 + ph, H=H, Wd=Wd, Kc=cin,
+                      alg_rows=self.N * H * Wd, alg_k=9.0 * cin / 4.0)
 
     # cross-attention with a single context token is a per-image vector: softmax over one key is 1, so
     # attn2(x, ctx) = to_out(to_v(ctx)) for every query (transformer.py:59-74 with Lk = 1).

@@ -44,3 +44,26 @@ def pack_geglu(w: torch.Tensor, b: torch.Tensor, bn: int):
     inner = w.shape[0] // 2
     perm = geglu_perm(inner, bn, w.device)
     return w.detach()[perm].to(torch.bfloat16).contiguous(), b.detach()[perm].float().contiguous()
+
+
+def pack_upconv_phases(w: torch.Tensor) -> list[torch.Tensor]:
+    """nn.Conv2d weight [Cout, Cin, 3, 3] of Upsample.conv (layers.py:42-46) -> four bf16 [Cout, 4*Cin] matrices, one per
+    output phase (py, px) in the order 2*py + px, columns (ty*2 + tx)*Cin + c.
+
+    out[2y+py, 2x+px] of conv3x3(nearest2x(v)) only sees v[y+py-1 .. y+py, x+px-1 .. x+px]: the three kernel rows fall on two
+    source rows -- py = 0: {w0} on y-1, {w1 + w2} on y;  py = 1: {w0 + w1} on y, {w2} on y+1 -- and likewise the columns.
+    Sums are taken in fp32 before the bf16 rounding."""
+    cout, cin, kh, kw = w.shape
+    assert kh == 3 and kw == 3
+    w = w.detach().float()
+    rows = {0: (w[:, :, 0], w[:, :, 1] + w[:, :, 2]), 1: (w[:, :, 0] + w[:, :, 1], w[:, :, 2])}   # each [Cout, Cin, 3]
+    out = []
+    for py in (0, 1):
+        for px in (0, 1):
+            taps = []
+            for ty in (0, 1):
+                r = rows[py][ty]
+                cols = (r[:, :, 0], r[:, :, 1] + r[:, :, 2]) if px == 0 else (r[:, :, 0] + r[:, :, 1], r[:, :, 2])
+                taps += [cols[0], cols[1]]
+            out.append(torch.cat(taps, dim=1).to(torch.bfloat16).contiguous())
+    return out

@@ -340,6 +340,31 @@ def test_upsample_and_im2col(ops):
     assert rel_l2(got, ref) < 5e-3
 
 
+@pytest.mark.parametrize("N,h,w,Cin,Cout", [(2, 9, 12, 64, 128), (3, 18, 18, 128, 96), (1, 5, 7, 192, 64)])
+def test_upsample_conv_as_four_phase_convs(ops, N, h, w, Cin, Cout):
+    """Upsample.forward (layers.py:42-46): conv3x3(nearest2x(x)) as four 2x2-tap phase GEMMs on the source image
+    (SevaGemm.ntaps = 4, out_map = 2 + phase) vs the upsample-then-convolve statement in fp32."""
+    from seva_b200 import pack
+    from seva_b200.ops import make_gemm, run_gemm
+
+    g = torch.Generator(device="cuda").manual_seed(12)
+    x = bf(torch.randn(N, Cin, h, w, device="cuda", generator=g))
+    xp = F.pad(x.permute(0, 2, 3, 1), (0, 0, 1, 1, 1, 1)).reshape(-1, Cin).contiguous()
+    wt = torch.randn(Cout, Cin, 3, 3, device="cuda", generator=g) / math.sqrt(9 * Cin)
+    b = torch.randn(Cout, device="cuda", generator=g)
+    out = torch.zeros(N * (2 * h + 2) * (2 * w + 2), Cout, device="cuda", dtype=torch.bfloat16)
+    phases = pack.pack_upconv_phases(wt)
+    for ph in range(4):
+        gd = make_gemm(A_ptr=xp.data_ptr(), lda=Cin, a_rows=xp.shape[0], W_ptr=phases[ph].data_ptr(), ldw=4 * Cin,
+                       M=xp.shape[0], N=Cout, Kc=Cin, out_ptr=out.data_ptr(), ldo=Cout, ntaps=4, tap_wp=w + 2,
+                       bias_ptr=b.data_ptr(), out_map=2 + ph, H=h, Wd=w)
+        run_gemm(gd)
+    ref = F.conv2d(F.interpolate(x.float(), scale_factor=2, mode="nearest"), wt, b, padding=1)
+    o = out.reshape(N, 2 * h + 2, 2 * w + 2, Cout)
+    assert rel_l2(o[:, 1:-1, 1:-1].permute(0, 3, 1, 2), ref) < 6e-3
+    assert o[:, 0].abs().max() == 0 and o[:, -1].abs().max() == 0 and o[:, :, 0].abs().max() == 0 and o[:, :, -1].abs().max() == 0
+
+
 def test_gemm_out_map_compact_to_padded(ops):
     g = torch.Generator(device="cuda").manual_seed(9)
     n_img, H, Wd, K, N = 2, 6, 10, 64, 64
