@@ -118,3 +118,33 @@ for n_img, H, Cin, Cout, has_res in CONV:
                  o[:, :, -1].abs().max().item())
     print(f"{name:44s} {t * 1e3:8.1f} us  {2.0 * n_img * H * H * Cout * Cin * 9 / t / 1e9:7.1f} TF/s  relL2 {err:.2e} "
           f"border {border:.1e}", flush=True)
+
+# Upsample.forward as four phase convolutions (SevaGemm ntaps = 4, out_map = 2..5): (n_img, low-res H, Cin, Cout)
+UPCONV = [(42, 36, 640, 640), (42, 18, 1280, 1280), (42, 9, 1280, 1280)]
+for n_img, H, Cin, Cout in UPCONV:
+    name = f"upconv n{n_img} H{H}->{2 * H} Cin{Cin} Cout{Cout}"
+    if filt and filt not in name:
+        continue
+    Hp = H + 2
+    ximg = torch.zeros(n_img, Hp, Hp, Cin, device=dev)
+    ximg[:, 1:-1, 1:-1] = rnd(n_img, H, H, Cin)
+    x = ximg.reshape(-1, Cin).bfloat16()
+    Wc = rnd(Cout, Cin, 3, 3) / math.sqrt(9 * Cin)
+    phases = pack.pack_upconv_phases(Wc)
+    b = rnd(Cout) * 0.1
+    out = torch.zeros(n_img * (2 * H + 2) * (2 * H + 2), Cout, device=dev, dtype=torch.bfloat16)
+    gs = [ops.make_gemm(A_ptr=x.data_ptr(), lda=Cin, a_rows=x.shape[0], W_ptr=phases[ph].data_ptr(), ldw=4 * Cin,
+                        M=x.shape[0], N=Cout, Kc=Cin, out_ptr=out.data_ptr(), ldo=Cout, ntaps=4, tap_wp=H + 2,
+                        bias_ptr=b.data_ptr(), out_map=2 + ph, H=H, Wd=H) for ph in range(4)]
+
+    def fn():
+        for g_ in gs:
+            ops.run_gemm(g_)
+
+    t = timeit(fn)
+    xi = x.reshape(n_img, Hp, Hp, Cin)[:2, 1:-1, 1:-1].permute(0, 3, 1, 2).float()
+    y = F.conv2d(F.interpolate(xi, scale_factor=2, mode="nearest"), Wc, b, padding=1).permute(0, 2, 3, 1)
+    o = out.reshape(n_img, 2 * H + 2, 2 * H + 2, Cout)
+    err = rel(o[:2, 1:-1, 1:-1], y)
+    print(f"{name:44s} {t * 1e3:8.1f} us  {2.0 * n_img * 4 * H * H * Cout * Cin * 9 / t / 1e9:7.1f} TF/s of reference FLOPs "
+          f"relL2 {err:.2e}", flush=True)

@@ -27,4 +27,6 @@ full gemm_conv_ds4    gemm_kernel 1 1 python tools/bench_gemm.py "conv3x3 n42 H1
 full attn_3d_ds2      attn_kernel 1 1 python tools/bench_attn.py 3d_ds2
 full attn_2d_ds1      attn_kernel 1 1 python tools/bench_attn.py 2d_ds1
 full gn               "gn_(stats|apply)" 5 2 python tools/bench_kernels.py gn
+full gn_finalize      gn_finalize 20 3 python bench.py --steps 1 --warmup 1 --no-cpu --no-gpu-baseline
+full upconv_ds1       gemm_kernel 1 1 python tools/bench_gemm.py "upconv"
 ls -la $OUT
