@@ -5,6 +5,7 @@
 // nn.GroupNorm eps=1e-6 at transformer.py:186, the dense scale/shift of ResBlock.forward
 // (layers.py:124-131), nn.LayerNorm at transformer.py:102-104,124,141-143.
 #include "common.cuh"
+#include <stdlib.h>
 #include "../../include/seva_b200.h"
 
 namespace seva {
@@ -514,6 +515,193 @@ gn_apply_dense_kernel(const GNApplyArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Dense (Plucker-modulated) apply on warp-level tensor cores.  The modulation of ResBlock.forward (layers.py:124-131),
+//   [scale, shift] = conv1x1(bilinear(plucker));  out = silu(gn(x)) * (1 + scale) + shift,
+// is a K = 6 (+ bias) GEMM per pixel: [16 pixels x 8] x [8 x 8 channels] per mma.sync.m16n8k8 (bf16 operands, fp32
+// accumulate -- the operand precision of the reference's autocast Conv2d).  Two chained MMAs per 8-channel block:
+//   D1 = P . Ws + 1          (accumulator initialised to 1: the "1 +" stays in fp32)
+//   v  = silu(a_c x + b_c) * D1
+//   D2 = P . Wh + v          (the final "+ shift" is the MMA's own accumulate)
+// so the 12 FMA per element of the scalar kernel above disappear from the FMA pipe.  A warp owns 32 channels and walks
+// 16-pixel tiles; the channel order inside the warp's slice is permuted so that a thread's accumulator columns are 8
+// CONTIGUOUS channels: one 16-byte load and one 16-byte store per pixel row, in exactly the fragment order (32-bit word j of
+// the row = columns of 8-channel block j).  The next tile's rows and Plucker values are fetched before the current tile's
+// arithmetic (register double buffer).  The block's warps cover adjacent 32-channel slices of the same pixels.
+// ------------------------------------------------------------------------------------------------
+constexpr int kMmaRing = 6;  // 16-pixel tiles in flight per thread
+
+__device__ __forceinline__ void mma_16x8x8_bf16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5}, {%6}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(b0));
+}
+
+__global__ void __launch_bounds__(640)
+gn_apply_dense_mma_kernel(const GNApplyArgs a) {
+  extern __shared__ float gstat[];  // [groups][2] mean, rstd
+  const int n = a.reverse ? gridDim.y - 1 - blockIdx.y : blockIdx.y;
+  const int bx = a.reverse ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+  const int cpg = a.C / a.groups;
+  const int HW = a.H * a.W;
+  const int Wp = a.W + 2;
+  const long long rpi_pad = (long long)(a.H + 2) * Wp;
+  for (int g = threadIdx.x; g < a.groups; g += blockDim.x) {
+    if (a.gstats != nullptr) {
+      const float2 v = __ldcg(reinterpret_cast<const float2*>(a.gstats) + (long long)n * a.groups + g);
+      gstat[2 * g] = v.x;
+      gstat[2 * g + 1] = v.y;
+      continue;
+    }
+    const float2* sp = reinterpret_cast<const float2*>(a.sums + ((long long)n * a.C + g * cpg) * 2);
+    float s = 0.f, q = 0.f;
+#pragma unroll 8
+    for (int c = 0; c < cpg; ++c) {
+      const float2 v = __ldcg(sp + c);
+      s += v.x;
+      q += v.y;
+    }
+    const double cnt = (double)cpg * (double)HW;
+    const double mean = (double)s / cnt;
+    const double var = fmax((double)q / cnt - mean * mean, 0.0);
+    gstat[2 * g] = (float)mean;
+    gstat[2 * g + 1] = (float)(1.0 / sqrt(var + (double)a.eps));
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, q = lane & 3;
+  const int cbase = blockIdx.z * a.cslice + warp * 32;  // this warp's 32 channels
+  const int c0 = cbase + q * 8;                          // this thread's 8 contiguous channels
+  f2_t sa[4], sb[4];                                     // GroupNorm affine of channel pairs (2j, 2j + 1)
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    float ta[2], tb[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int c = c0 + 2 * j + e;
+      const int g = c / cpg;
+      const float mean = gstat[2 * g], rstd = gstat[2 * g + 1];
+      ta[e] = rstd * __ldg(a.gamma + c);
+      tb[e] = fmaf(-mean, ta[e], __ldg(a.beta + c));
+    }
+    sa[j] = f2(ta[0], ta[1]);
+    sb[j] = f2(tb[0], tb[1]);
+  }
+  // B fragments: column gid of 8-channel block j is channel cbase + (gid / 2) * 8 + 2 j + (gid % 2); rows k = 2q, 2q + 1 of
+  // [w_0 .. w_5, bias, 0]
+  uint32_t bs[4], bh[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int ch = cbase + (gid >> 1) * 8 + 2 * j + (gid & 1);
+    float ws0, ws1, wh0, wh1;
+    if (q < 3) {
+      const float2 u = __ldg(reinterpret_cast<const float2*>(a.dense_w + (long long)ch * 6 + 2 * q));
+      const float2 v = __ldg(reinterpret_cast<const float2*>(a.dense_w + (long long)(a.C + ch) * 6 + 2 * q));
+      ws0 = u.x; ws1 = u.y; wh0 = v.x; wh1 = v.y;
+    } else {
+      ws0 = __ldg(a.dense_b + ch); ws1 = 0.f;
+      wh0 = __ldg(a.dense_b + a.C + ch); wh1 = 0.f;
+    }
+    bs[j] = pack_bf16x2(ws0, ws1);
+    bh[j] = pack_bf16x2(wh0, wh1);
+  }
+
+  const int p_begin = bx * a.pix_per_block;
+  const int p_end = min(HW, p_begin + a.pix_per_block);
+  const long long in_img = a.in_padded ? (long long)n * rpi_pad : (long long)n * HW;
+  const long long out_img = a.out_padded ? (long long)n * rpi_pad : (long long)n * HW;
+  const float* dn = a.dense + (long long)n * HW * 6 + 2 * q;
+  auto row_of = [&](int p, bool padded) -> long long {
+    if (!padded) return p;
+    const int y = (int)__umulhi((unsigned)p, a.w_magic);
+    return (long long)p + 2 * y + Wp + 1;  // (y + 1) * Wp + x + 1
+  };
+  // Row loads: every thread keeps kMmaRing tiles (2 rows x 16 bytes each) of its own channel vector in flight in shared
+  // memory (cp.async, zero-filled past the block's last pixel) and only ever reads what it copied itself: 20 warps x
+  // kMmaRing x 1 KB per SM in flight.  With a register double buffer alone (1 tile ahead, 20 KB per SM) the kernel sat at
+  // 2.4 TB/s = bytes in flight / HBM latency.
+  const uint32_t ring = smem_u32(gstat) + ((2 * a.groups * 4 + 15) & ~15) + threadIdx.x * 32;
+  const uint32_t ring_pitch = blockDim.x * 32;
+  auto issue = [&](int tile, int slot) {
+    const int p0 = tile + gid, p1 = p0 + 8;
+    const bool v0 = p0 < p_end, v1 = p1 < p_end;
+    const __nv_bfloat16* s0 = a.x + (in_img + row_of(v0 ? p0 : p_begin, a.in_padded)) * a.ldx + c0;
+    const __nv_bfloat16* s1 = a.x + (in_img + row_of(v1 ? p1 : p_begin, a.in_padded)) * a.ldx + c0;
+    const uint32_t dst = ring + slot * ring_pitch;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(s0), "r"(v0 ? 16 : 0) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst + 16), "l"(s1), "r"(v1 ? 16 : 0) : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  auto fetch_a = [&](int tile, uint32_t& a0, uint32_t& a1) {
+    const int p0 = tile + gid, p1 = p0 + 8;
+    float2 d0 = make_float2(1.f, 0.f), d1 = d0;   // q == 3: the bias row and the zero row
+    if (q < 3 && p0 < p_end) d0 = __ldg(reinterpret_cast<const float2*>(dn + (long long)p0 * 6));
+    if (q < 3 && p1 < p_end) d1 = __ldg(reinterpret_cast<const float2*>(dn + (long long)p1 * 6));
+    a0 = pack_bf16x2(d0.x, d0.y);
+    a1 = pack_bf16x2(d1.x, d1.y);
+  };
+  const f2_t half2 = f2(0.5f, 0.5f);
+#pragma unroll
+  for (int d = 0; d < kMmaRing; ++d) issue(p_begin + 16 * d, d);
+  uint32_t a0c, a1c, a0n = 0, a1n = 0;
+  fetch_a(p_begin, a0c, a1c);
+  int slot = 0;
+  for (int tile = p_begin; tile < p_end; tile += 16) {
+    if (tile + 16 < p_end) fetch_a(tile + 16, a0n, a1n);
+    asm volatile("cp.async.wait_group %0;" ::"n"(kMmaRing - 1) : "memory");
+    uint32_t xw0[4], xw1[4];
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(xw0[0]), "=r"(xw0[1]), "=r"(xw0[2]), "=r"(xw0[3]) : "r"(ring + slot * ring_pitch) : "memory");
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(xw1[0]), "=r"(xw1[1]), "=r"(xw1[2]), "=r"(xw1[3]) : "r"(ring + slot * ring_pitch + 16) : "memory");
+    issue(tile + 16 * kMmaRing, slot);   // refill the slot just consumed (all-invalid tiles past the end are zero fills)
+    slot = slot + 1 == kMmaRing ? 0 : slot + 1;
+    uint32_t o0[4], o1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float d[4] = {1.f, 1.f, 1.f, 1.f};
+      mma_16x8x8_bf16(d, a0c, a1c, bs[j]);  // 1 + scale
+      f2_t h0 = f2fma(f2(bf16_lo(xw0[j]), bf16_hi(xw0[j])), sa[j], sb[j]);
+      f2_t h1 = f2fma(f2(bf16_lo(xw1[j]), bf16_hi(xw1[j])), sa[j], sb[j]);
+      if (a.silu) {  // x * sigmoid(x), sigmoid(x) = 0.5 * tanh(0.5 x) + 0.5
+        const f2_t g0 = f2mul(h0, half2), g1 = f2mul(h1, half2);
+        h0 = f2mul(h0, f2fma(f2(fast_tanh(f2lo(g0)), fast_tanh(f2hi(g0))), half2, half2));
+        h1 = f2mul(h1, f2fma(f2(fast_tanh(f2lo(g1)), fast_tanh(f2hi(g1))), half2, half2));
+      }
+      const f2_t v0 = f2mul(h0, f2(d[0], d[1])), v1 = f2mul(h1, f2(d[2], d[3]));
+      float e[4] = {f2lo(v0), f2hi(v0), f2lo(v1), f2hi(v1)};
+      mma_16x8x8_bf16(e, a0c, a1c, bh[j]);  // + shift
+      o0[j] = pack_bf16x2(e[0], e[1]);
+      o1[j] = pack_bf16x2(e[2], e[3]);
+    }
+    const int p0 = tile + gid, p1 = p0 + 8;
+    if (p0 < p_end)
+      *reinterpret_cast<uint4*>(a.y + (out_img + row_of(p0, a.out_padded)) * a.ldy + c0) = make_uint4(o0[0], o0[1], o0[2], o0[3]);
+    if (p1 < p_end)
+      *reinterpret_cast<uint4*>(a.y + (out_img + row_of(p1, a.out_padded)) * a.ldy + c0) = make_uint4(o1[0], o1[1], o1[2], o1[3]);
+    a0c = a0n;
+    a1c = a1n;
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+  // zero border of a padded output image (first pixel block of each image), this block's channel slice
+  if (a.out_padded && bx == 0) {
+    const int Hp = a.H + 2;
+    const int nborder = 2 * Wp + 2 * a.H;
+    const int vecs = a.cslice / 8;
+    for (int i = threadIdx.x; i < nborder * vecs; i += blockDim.x) {
+      const int b = i / vecs, v = i - b * vecs;
+      int yy, xx;
+      if (b < Wp) { yy = 0; xx = b; }
+      else if (b < 2 * Wp) { yy = Hp - 1; xx = b - Wp; }
+      else { const int k = b - 2 * Wp; yy = 1 + (k >> 1); xx = (k & 1) ? Wp - 1 : 0; }
+      const long long row = out_img + (long long)yy * Wp + xx;
+      *reinterpret_cast<uint4*>(a.y + row * a.ldy + blockIdx.z * a.cslice + v * 8) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // GroupNorm finalize: folds the per-32-row-block partial statistics that the PRODUCING GEMM's epilogue wrote
 // (SevaGemm.gn_partial) into per-(image, group) mean / rstd.  Up to two sources side by side along the channel axis
 // (the virtual skip concat of the decoder: each producer has its own row space and slot count; groups may straddle
@@ -811,6 +999,15 @@ extern "C" int seva_groupnorm_finalize(const float* part0, int32_t C0, int32_t r
   return 0;
 }
 
+static bool gn_dense_scalar_forced() {
+#ifdef SEVA_DEBUG
+  static const bool f = [] { const char* e = getenv("SEVA_GN_DENSE_SCALAR"); return e && atoi(e) != 0; }();
+  return f;
+#else
+  return false;
+#endif
+}
+
 extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   using namespace seva;
   if (check_device()) return 3;
@@ -824,6 +1021,9 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   SEVA_CHECK(!p->dense || ((uintptr_t)p->dense & 7) == 0, "seva_groupnorm_apply: dense must be 8-byte aligned");
   GNApplyArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(p->x);
+  const bool dense_mma = p->dense && (p->C % 32) == 0 && (p->ldx % 8) == 0 && (p->ldy % 8) == 0 &&
+                         (((uintptr_t)p->x | (uintptr_t)p->y) & 15) == 0 && ((uintptr_t)p->dense_w & 7) == 0 &&
+                         ((uintptr_t)p->dense & 7) == 0 && !gn_dense_scalar_forced();
   a.ldx = p->ldx;
   a.y = reinterpret_cast<__nv_bfloat16*>(p->y);
   a.ldy = p->ldy;
@@ -845,6 +1045,58 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
   a.reverse = p->reverse != 0;
   // dense modulation keeps 4x2x6 weights per thread in registers -> 4-channel vectors (8-byte accesses);
   // the plain path uses 8-channel vectors (16-byte accesses) when the strides allow it
+  if (dense_mma) {
+    // Launch shape: warps per block (= adjacent 32-channel slices a block covers: a divisor of C / 32, at most 20, at least 4
+    // where the channel count allows so that a block's rows stay >= 256 contiguous bytes) and pixel blocks per image, chosen
+    // together against a small cost model -- whole waves of the resident block slots (a 1.4-wave grid ran at 71 % of a
+    // 2-wave one), ~8 tiles of fixed cost per block (statistics, weight fragments, ring warm-up and drain), and per-tile time
+    // falling with the resident warps up to 20 per SM.
+    const int slices = p->C / 32;
+    const int HWp = p->H * p->Wd;
+    a.w_magic = (unsigned)((0x100000000ull + (unsigned)p->Wd - 1) / (unsigned)p->Wd);
+    SEVA_CHECK((unsigned long long)HWp * p->Wd < 0x100000000ull, "seva_groupnorm_apply: image too large");
+    if (ensure_dyn_smem(reinterpret_cast<const void*>(gn_apply_dense_mma_kernel), 160 * 1024)) return 2;
+    const size_t stat_bytes = (sizeof(float) * 2 * p->groups + 15) & ~(size_t)15;
+    const long long tiles = (HWp + 15) / 16;
+    const long long max_gx = HWp / 64 > 0 ? HWp / 64 : 1;
+    bool any4 = false;
+    for (int d = 4; d <= 20; ++d) any4 = any4 || (slices % d == 0);
+    int wpb = 1;
+    long long gx = 1;
+    double best = -1.0;
+    for (int d = any4 ? 4 : 1; d <= 20; ++d) {
+      if (slices % d) continue;
+      int resident = 0;
+      SEVA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, gn_apply_dense_mma_kernel, d * 32,
+                                                            stat_bytes + (size_t)kMmaRing * d * 32 * 32));
+      if (resident < 1) continue;
+      const long long slots = (long long)sm_count() * resident;
+      const long long per_gx = (long long)p->Nimg * (slices / d);
+      const int W = resident * d;
+      const double per_tile = W >= 20 ? W / 20.0 : 20.0 / W;
+      for (long long g = 1; g <= max_gx && g <= 256; ++g) {
+        const long long waves = (g * per_gx + slots - 1) / slots;
+        const long long tpb = (tiles + g - 1) / g;
+        const double cost = (double)waves * (double)(tpb + 8) * per_tile;
+        if (best < 0.0 || cost < best - 1e-9) {
+          best = cost;
+          wpb = d;
+          gx = g;
+        }
+      }
+    }
+    SEVA_CHECK(best >= 0.0, "seva_groupnorm_apply: no launch shape for C=%d", p->C);
+    const int nz = slices / wpb;
+    a.cslice = wpb * 32;
+    const size_t smem_m = stat_bytes + (size_t)kMmaRing * wpb * 32 * 32;
+    int ppb = (int)((HWp + gx - 1) / gx);
+    ppb = (ppb + 15) / 16 * 16;
+    a.pix_per_block = ppb;
+    dim3 grid((HWp + ppb - 1) / ppb, p->Nimg, nz);
+    gn_apply_dense_mma_kernel<<<grid, wpb * 32, smem_m, stream>>>(a);
+    SEVA_CUDA(cudaGetLastError());
+    return 0;
+  }
   const bool vec8 = !p->dense && (p->C % 8) == 0 && (p->ldx % 8) == 0 && (p->ldy % 8) == 0 &&
                     (((uintptr_t)p->x | (uintptr_t)p->y) & 15) == 0;
   const int vec = vec8 ? 8 : 4;

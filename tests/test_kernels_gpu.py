@@ -280,7 +280,10 @@ def test_groupnorm(ops, n_img, H, Wd, Cc, in_pad, out_pad, silu, dense):
     if silu:
         ref = F.silu(ref)
     if dense:
-        d = torch.einsum("npk,ck->ncp", dmap, dw).reshape(n_img, 2 * Cc, H, Wd) + db[None, :, None, None]
+        # the 1x1 modulation conv runs on bf16 operands with fp32 accumulation, as the reference's Conv2d does under
+        # torch.autocast (layers.py:124-128); the comparison rounds the operands the same way
+        d = (torch.einsum("npk,ck->ncp", bf(dmap).float(), bf(dw).float()).reshape(n_img, 2 * Cc, H, Wd)
+             + bf(db).float()[None, :, None, None])
         sc, sh = d.chunk(2, dim=1)
         ref = ref * (1 + sc) + sh
     if out_pad:
