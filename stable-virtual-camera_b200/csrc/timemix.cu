@@ -222,56 +222,67 @@ __device__ __forceinline__ uint32_t tm_off(int row, int chunk) {
 // KT = number of 32-row blocks along the frame axis: KT = 1 serves T <= 32 (the T = 21 default), KT = 2 serves
 // T <= 64 (BASELINE configs[4]); query blocks are processed one after the other against all KT key blocks.
 template <int KT>
-__global__ void __launch_bounds__(kTmmWarps * 32, KT == 1 ? 4 : 2)
+__global__ void __launch_bounds__(kTmmWarps * 32, 2)
 timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __restrict__ kp,
                    const __nv_bfloat16* __restrict__ vp, __nv_bfloat16* __restrict__ out, int B, int Tq, int T,
                    int S, int Hh, long long ldq, long long ldkv, long long ldo, float scale_log2, long long total,
                    long long nwarps_total) {
   extern __shared__ __align__(128) uint8_t tm_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t qS = smem_u32(tm_smem) + warp * (KT * kTmmBytes);
-  const uint32_t kS = qS + KT * 4096, vS = qS + 2 * KT * 4096;
+  // Q, K, V tiles of an item are staged with cp.async; with two buffers per warp (KT = 1) the next item's 63 row segments
+  // are in flight while the current item is computed: 8 KB per warp in flight all the time instead of 4 KB during the
+  // load phase only (the single-buffer kernel sat at 2.5 TB/s = bytes in flight / HBM latency at 16 warps per SM).
+  constexpr int NB = KT == 1 ? 2 : 1;
+  const uint32_t warp_base = smem_u32(tm_smem) + warp * (NB * KT * kTmmBytes);
   const int sub = lane >> 3, part = lane & 7;  // staging: 8 lanes x 16 B per row, 4 rows per instruction
   const int g = lane >> 2, q4 = lane & 3;      // fragment coordinates
   // rows >= T stay zero for the whole kernel (V rows meet P = 0 there: they must be finite)
-  for (int i = lane; i < KT * kTmmBytes / 16; i += 32)
-    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(qS + i * 16), "r"(0u) : "memory");
+  for (int i = lane; i < NB * KT * kTmmBytes / 16; i += 32)
+    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(warp_base + i * 16), "r"(0u) : "memory");
   __syncwarp();
-
-  for (long long item = (long long)blockIdx.x * kTmmWarps + warp; item < total; item += nwarps_total) {
+  auto stage = [&](long long item, uint32_t qS) {
+    const uint32_t kS = qS + KT * 4096, vS = qS + 2 * KT * 4096;
     const int h = (int)(item % Hh);
     const long long bs = item / Hh;
     const int s = (int)(bs % S);
     const int b = (int)(bs / S);
-    // ---- stage Q, K, V: two rounds of 16 rows, each with its 12 row loads issued before the stores
-    __syncwarp();  // the previous item's output staging has been read
 #pragma unroll
-    for (int half = 0; half < 2 * KT; ++half) {
-      if (half * 16 < T || half * 16 < Tq) {
-        uint4 lq[4], lk[4], lv[4];
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int t = half * 16 + 4 * r + sub;
-          if (t < Tq)
-            lq[r] = __ldg(reinterpret_cast<const uint4*>(qp + (((long long)b * Tq + t) * S + s) * ldq + h * 64 + part * 8));
-          if (t < T) {
-            const long long off = (((long long)b * T + t) * S + s) * ldkv + h * 64 + part * 8;
-            lk[r] = __ldg(reinterpret_cast<const uint4*>(kp + off));
-            lv[r] = __ldg(reinterpret_cast<const uint4*>(vp + off));
-          }
-        }
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int t = half * 16 + 4 * r + sub;
-          const uint32_t o = tm_off(t, part);
-          if (t < Tq)
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(qS + o), "r"(lq[r].x), "r"(lq[r].y), "r"(lq[r].z), "r"(lq[r].w) : "memory");
-          if (t < T) {
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(kS + o), "r"(lk[r].x), "r"(lk[r].y), "r"(lk[r].z), "r"(lk[r].w) : "memory");
-            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(vS + o), "r"(lv[r].x), "r"(lv[r].y), "r"(lv[r].z), "r"(lv[r].w) : "memory");
-          }
-        }
+    for (int r = 0; r < 8 * KT; ++r) {
+      const int t = 4 * r + sub;
+      const uint32_t o = tm_off(t, part);
+      if (t < Tq)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(qS + o),
+                     "l"(qp + (((long long)b * Tq + t) * S + s) * ldq + h * 64 + part * 8) : "memory");
+      if (t < T) {
+        const long long off = (((long long)b * T + t) * S + s) * ldkv + h * 64 + part * 8;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(kS + o), "l"(kp + off) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(vS + o), "l"(vp + off) : "memory");
       }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const long long first = (long long)blockIdx.x * kTmmWarps + warp;
+  if (first < total) stage(first, warp_base);
+  int cur = 0;
+
+  for (long long item = first; item < total; item += nwarps_total) {
+    const int h = (int)(item % Hh);
+    const long long bs = item / Hh;
+    const int s = (int)(bs % S);
+    const int b = (int)(bs / S);
+    const uint32_t qS = warp_base + cur * (KT * kTmmBytes);
+    const uint32_t kS = qS + KT * 4096, vS = qS + 2 * KT * 4096;
+    __syncwarp();  // every lane is done with the buffer the next stage overwrites (its output rows were stored)
+    if (NB == 2) {
+      if (item + nwarps_total < total) {
+        stage(item + nwarps_total, warp_base + (cur ^ 1) * (KT * kTmmBytes));
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      } else {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      cur ^= 1;
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncwarp();
 
@@ -389,6 +400,10 @@ timemix_mma_kernel(const __nv_bfloat16* __restrict__ qp, const __nv_bfloat16* __
     }
     // rows >= T of the Q tile were overwritten by the padded query rows' outputs: harmless (Q rows >= T only
     // produce rows >= T), but they must stay finite: they are bf16 of finite values.
+    if (NB == 1 && item + nwarps_total < total) {
+      __syncwarp();
+      stage(item + nwarps_total, warp_base);
+    }
   }
 }
 
@@ -402,10 +417,10 @@ struct TmArgs {
 
 template <int KT>
 int launch_timemix_mma(const TmArgs& a, cudaStream_t stream) {
-  const size_t smem = (size_t)kTmmWarps * KT * kTmmBytes;
+  const size_t smem = (size_t)kTmmWarps * (KT == 1 ? 2 : 1) * KT * kTmmBytes;
   if (ensure_dyn_smem(reinterpret_cast<const void*>(timemix_mma_kernel<KT>), (int)smem)) return 2;
   const long long total = (long long)a.B * a.S * a.Hh;
-  long long grid = (KT == 1 ? 4ll : 2ll) * sm_count();  // resident blocks per SM, each warp striding over items
+  long long grid = 2ll * sm_count();  // resident blocks per SM (96 KB of tiles each), each warp striding over items
   const long long need = (total + kTmmWarps - 1) / kTmmWarps;
   if (grid > need) grid = need;
   timemix_mma_kernel<KT><<<(unsigned)grid, kTmmWarps * 32, smem, stream>>>(a.q, a.k, a.v, a.out, a.B, a.Tq, a.Tk,
