@@ -5,6 +5,7 @@
 // nn.GroupNorm eps=1e-6 at transformer.py:186, the dense scale/shift of ResBlock.forward
 // (layers.py:124-131), nn.LayerNorm at transformer.py:102-104,124,141-143.
 #include "common.cuh"
+#include <mutex>
 #include <stdlib.h>
 #include "../../include/seva_b200.h"
 
@@ -999,6 +1000,24 @@ extern "C" int seva_groupnorm_finalize(const float* part0, int32_t C0, int32_t r
   return 0;
 }
 
+// resident blocks per SM of the mma apply kernel for `warps` warps per block: the occupancy query costs ~100 us on the host,
+// so it is made once per (device, warps); thread-safe
+static int gn_mma_resident(int warps, size_t smem) {
+  static std::mutex mu;
+  static int cache[16][21];  // [device][warps], 0 = not asked yet, -1 = does not fit
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (dev < 0 || dev >= 16 || warps < 1 || warps > 20) return 0;
+  if (cache[dev][warps] == 0) {
+    int r = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r, seva::gn_apply_dense_mma_kernel, warps * 32, smem) != cudaSuccess)
+      r = 0;
+    cache[dev][warps] = r > 0 ? r : -1;
+  }
+  return cache[dev][warps] > 0 ? cache[dev][warps] : 0;
+}
+
 static bool gn_dense_scalar_forced() {
 #ifdef SEVA_DEBUG
   static const bool f = [] { const char* e = getenv("SEVA_GN_DENSE_SCALAR"); return e && atoi(e) != 0; }();
@@ -1066,9 +1085,7 @@ extern "C" int seva_groupnorm_apply(const SevaGNApply* p, void* stream_v) {
     double best = -1.0;
     for (int d = any4 ? 4 : 1; d <= 20; ++d) {
       if (slices % d) continue;
-      int resident = 0;
-      SEVA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, gn_apply_dense_mma_kernel, d * 32,
-                                                            stat_bytes + (size_t)kMmaRing * d * 32 * 32));
+      const int resident = gn_mma_resident(d, stat_bytes + (size_t)kMmaRing * d * 32 * 32);
       if (resident < 1) continue;
       const long long slots = (long long)sm_count() * resident;
       const long long per_gx = (long long)p->Nimg * (slices / d);
