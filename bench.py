@@ -306,12 +306,44 @@ def run_ours(args):
         ms_inst = maxed(e0.elapsed_time(e1))
         eng.timing_sink = None
         # ---- end-to-end timing: host buffers in, host result out, every step ---------------------
+        # Every step's inputs come from pinned host memory and its result goes back to the host, all inside the timed
+        # region.  Two preallocated device input sets: the upload of step i + 1 runs on a copy stream while step i
+        # computes (what a serving loop does); the compute stream waits for its own step's upload, the copy stream for the
+        # step that last read the set it overwrites.  The conditioning changes identity every step, so the guider's
+        # prepared-input cache and the engine's step-invariant hoisting are OFF on this path (every step pays them).
+        main = torch.cuda.current_stream()
+        copy_stream = torch.cuda.Stream()
+        flat = lambda t6: [t6[0], *t6[1].values(), *t6[2].values(), *t6[3:]]
+        host_flat = flat((host["x0"], host["c"], host["uc"], host["c2w"], host["K"], host["mask"]))
+        sets = [upload() for _ in range(2)]
+        torch.cuda.synchronize()
+        uploaded = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+
+        def upload_into(k, first):
+            with torch.cuda.stream(copy_stream):
+                if not first:
+                    copy_stream.wait_event(consumed[k])
+                for dst, src in zip(flat(sets[k]), host_flat):
+                    dst.copy_(src, non_blocking=True)
+                uploaded[k].record(copy_stream)
+
+        def e2e_steps(n):
+            upload_into(0, True)
+            for i in range(n):
+                k = i % 2
+                main.wait_event(uploaded[k])
+                if i + 1 < n:
+                    upload_into(1 - k, i == 0)
+                xh, c_, uc_, c2w_, K_, mask_ = sets[k]
+                xn = step(i, xh * 84.9222, c_, uc_, c2w_, K_, mask_)
+                consumed[k].record(main)
+                x_host.copy_(xn, non_blocking=True)
+
+        e2e_steps(2)  # untimed: this path's own launch variant (no hoisting) is captured into its CUDA graph here
         barrier()
         e0.record()
-        for i in range(args.steps):
-            xh, c, uc, c2w, K, mask = upload()
-            xn = step(i, xh * 84.9222, c, uc, c2w, K, mask)
-            x_host.copy_(xn, non_blocking=True)
+        e2e_steps(args.steps)
         e1.record()
         barrier()
         ms_e2e = maxed(e0.elapsed_time(e1))
