@@ -261,6 +261,13 @@ int seva_timestep_embedding(const int64_t* t, float* out, int32_t N, int32_t dim
 int seva_gemv_rows(const float* x, const void* W, const float* bias, float* out, int32_t M,
                    int32_t N, int32_t K, int32_t silu_in, int32_t silu_out, void* stream);
 
+/* `emb_layers(time_embed(timestep_embedding(t)))` (seva/modules/layers.py:11-32,102-105,134; seva/model.py:185-186)
+ * depends on the sigma index only, so its rows for every index are kept in a table [table_rows][ld] (fp32) and a step only
+ * gathers: block (n, i) copies table[t[n]][col_off_i : +cout_i] to dst_i[n][0 : cout_i].  desc: DEVICE array [nb][3] of int64
+ * (col_off, cout, destination pointer); cout and col_off multiples of 4.  t must lie in [0, table_rows). */
+int seva_emb_gather(const float* table, int64_t ld, int32_t table_rows, const int64_t* t, int32_t N, const int64_t* desc,
+                    int32_t nb, void* stream);
+
 /* Grouped form of seva_gemv_rows: `count` independent problems described by a table in DEVICE memory
  * (K multiple of 8; every problem's M, N, K bounded by max_M, max_N, max_K). */
 typedef struct SevaGemvProblem {

@@ -538,6 +538,21 @@ inline unsigned blocks_for(long long total, int threads) {
   return (unsigned)((total + threads - 1) / threads);
 }
 
+// Rows of a precomputed per-timestep table -> the per-ResBlock row-bias buffers of a step: block (n, i) copies
+// table[t[n]][col_off_i : col_off_i + cout_i] to dst_i[n][0 : cout_i].  desc = [nb][3] int64 (col_off, cout, dst pointer).
+__global__ void __launch_bounds__(128)
+emb_gather_kernel(const float* __restrict__ table, long long ld, const int64_t* __restrict__ t, int table_rows,
+                  const long long* __restrict__ desc) {
+  const int n = blockIdx.x;
+  const long long* d = desc + 3ll * blockIdx.y;
+  const long long col = d[0], cout = d[1];
+  float* dst = reinterpret_cast<float*>(d[2]) + (long long)n * cout;
+  long long row = t[n];
+  row = row < 0 ? 0 : (row >= table_rows ? table_rows - 1 : row);  // callers guarantee the range; never read outside
+  const float4* src = reinterpret_cast<const float4*>(table + row * ld + col);
+  for (int i = threadIdx.x; i < cout / 4; i += blockDim.x) reinterpret_cast<float4*>(dst)[i] = __ldg(src + i);
+}
+
 }  // namespace
 }  // namespace seva
 
@@ -716,6 +731,16 @@ extern "C" int seva_cast_f32_bf16(const float* src, void* dst, int64_t n, void* 
   SEVA_CHECK(src && dst && n > 0, "seva_cast_f32_bf16: bad arguments");
   cast_f32_bf16_kernel<<<blocks_for(n, 256), 256, 0, stream>>>(src, reinterpret_cast<__nv_bfloat16*>(dst),
                                                               n);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int seva_emb_gather(const float* table, int64_t ld, int32_t table_rows, const int64_t* t, int32_t N,
+                               const int64_t* desc, int32_t nb, void* stream_v) {
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(table && t && desc && N > 0 && nb > 0 && table_rows > 0 && (ld % 4) == 0, "seva_emb_gather: bad arguments");
+  emb_gather_kernel<<<dim3(N, nb), 128, 0, stream>>>(table, ld, t, table_rows, reinterpret_cast<const long long*>(desc));
   SEVA_CUDA(cudaGetLastError());
   return 0;
 }

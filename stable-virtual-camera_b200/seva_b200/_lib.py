@@ -87,6 +87,7 @@ _PROTOS = {
     "seva_timestep_embedding": [c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
     "seva_gemv_grouped": [c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "seva_gemv_rows": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "seva_emb_gather": [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p],
     "seva_resize_bicubic_aa": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "seva_clip_patchify": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, C.POINTER(c_float), C.POINTER(c_float),
                            c_void_p],

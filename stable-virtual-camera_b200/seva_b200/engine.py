@@ -442,6 +442,15 @@ class Engine:
         # Step-invariant hoisting: launches that read only the conditioning (Plucker resizes, Lk = 1
         # cross-attention vectors) are skipped while ``bind`` is handed the same conditioning epoch as last time.
         self._invariant: set = set()
+        # launches that depend on the timestep only (t-emb, time_embed, emb_layers): with the per-index table (N2) a step
+        # runs ONE gather instead; see _build_emb_table
+        self._emb_calls: set = set()
+        self._emb_outs: list = []
+        self._emb_gather_idx = None
+        self._emb_table = None
+        self._emb_rows = 0
+        self._use_emb_table = False
+        self.emb_table_enabled = os.environ.get("SEVA_EMB_TABLE", "1") != "0"
         self._epoch = None
         self._skip_invariant = False
         # The plan is static (constant pointers and sizes), so after one eager run per variant (all launches / the
@@ -635,9 +644,26 @@ class Engine:
             self.meta.insert(pos, ("seva_gemv_grouped", name, 0.0, 0.0))
             self.n_launch += 1
             self._invariant = {i + 1 if i >= pos else i for i in self._invariant}
+            self._emb_calls = {i + 1 if i >= pos else i for i in self._emb_calls}
             if name != "emb":  # the cross-attention vectors depend on the context only, not on the step
                 self._invariant.add(pos)
+            else:
+                self._emb_calls.add(pos)
             pos += 1
+        if self._emb_outs:
+            # the table path's only launch: rows of the per-index table -> the ResBlocks' row-bias buffers
+            desc = torch.zeros(len(self._emb_outs), 3, dtype=torch.int64)
+            col = 0
+            for i, (buf, cout) in enumerate(self._emb_outs):
+                desc[i, 0], desc[i, 1], desc[i, 2] = col, cout, buf.data_ptr()
+                col += cout
+            self._emb_desc = desc.to(self.dev)
+            self._emb_cols = col
+            self._emb_gather_idx = pos
+            self.calls.insert(pos, (None, ()))   # filled in when the table exists; skipped until then
+            self.meta.insert(pos, ("seva_emb_gather", "emb table", 0.0, 0.0))
+            self._invariant = {i + 1 if i >= pos else i for i in self._invariant}
+            self._emb_calls = {i + 1 if i >= pos else i for i in self._emb_calls}
 
     # ---- network -------------------------------------------------------------------------------
     def _build(self, model: Seva):
@@ -649,6 +675,7 @@ class Engine:
         e1 = self.buf("temb1", N, ted, F32)
         self.emb = self.buf("emb", N, ted, F32)
         te = self.P["time_embed"]
+        self._emb_calls.update(range(len(self.calls), len(self.calls) + 3))
         self.add(lib.seva_timestep_embedding, self.t_in.data_ptr(), temb.data_ptr(), N, mc, 10000.0)
         self.gemv(temb, te["w0"], te["b0"], e1, silu_out=True)
         # ``emb`` is consumed only through ``emb_layers = Sequential(SiLU, Linear)`` (layers.py:102-105): the SiLU is
@@ -746,6 +773,7 @@ class Engine:
                 dense_b=w["bd"])
         emb_out = self.buf(f"rb_emb_{id(m)}", self.N, cout, F32)
         self.gemv(self.emb, w["we"], w["be"], emb_out, group="emb")
+        self._emb_outs.append((emb_out, cout))
         h2 = self.buf(f"rb_h2_{l}", rp, cout)
         self.conv3x3(h1, l, w["w1"], w["cb1"], h2, rowbias=emb_out)
         h3 = self.buf(f"rb_h3_{l}", rp, cout)
@@ -998,13 +1026,18 @@ class Engine:
         return epoch is not None and epoch == self._epoch
 
     def bind(self, t: torch.Tensor, ctx: torch.Tensor | None, dense: torch.Tensor | None,
-             ctx0: torch.Tensor | None = None, epoch=None) -> None:
+             ctx0: torch.Tensor | None = None, epoch=None, t_range: int = 0) -> None:
         """Copy the per-call conditioning into the plan's static input buffers (device-to-device).  ``ctx0`` is
         ``context[::T]`` (transformer.py:222-229); a frame shard passes the full batch's, since frame 0 may live
         on another rank.  ``epoch`` (from the guider's ``prepare_inputs`` cache, one value per sampling loop and
         conditioning) marks ctx / dense as unchanged since the last call with the same value: they are not copied
         again and the launches that depend only on them are skipped by ``run``."""
         self.t_in.copy_(t.reshape(-1))
+        # ``t_range`` > 0: the caller guarantees 0 <= t < t_range (the denoiser's sigma indices, sampling.py:126-131), so the
+        # timestep-only launches may be served from the per-index table
+        self._use_emb_table = bool(t_range) and self.emb_table_enabled and self._emb_gather_idx is not None
+        if self._use_emb_table and (self._emb_table is None or self._emb_rows != t_range):
+            self._build_emb_table(int(t_range))
         if self.cond_current(epoch):
             self._skip_invariant = True
             return
@@ -1017,7 +1050,36 @@ class Engine:
     @property
     def n_launch_step(self) -> int:
         """Launches of a step whose conditioning is already bound."""
-        return self.n_launch - len(self._invariant)
+        return self.n_launch - len(self._invariant) - (len(self._emb_calls) - 1 if self._use_emb_table else 0)
+
+    def _build_emb_table(self, rows: int) -> None:
+        """N2: ``emb_layers(time_embed(timestep_embedding(t)))`` for every sigma index, computed ONCE per engine with the
+        plan's own launches (N indices at a time, so every table row is bit-identical to what a step would compute), kept as
+        fp32 [rows, sum of the ResBlocks' widths] (80 MB at the released size).  A step then gathers its rows
+        (``seva_emb_gather``) instead of running the t-emb kernel, two GEMVs and the grouped GEMV."""
+        stream = torch.cuda.current_stream().cuda_stream
+        table = torch.empty(rows, self._emb_cols, device=self.dev, dtype=F32)
+        saved = self.t_in.clone()
+        order = sorted(self._emb_calls)
+        for r0 in range(0, rows, self.N):
+            n = min(self.N, rows - r0)
+            self.t_in.copy_(torch.arange(r0, r0 + self.N, device=self.dev).clamp_(max=rows - 1))
+            for i in order:
+                fn, args = self.calls[i]
+                rc = fn(*args, stream)
+                if rc != 0:
+                    raise SevaB200Error(f"{fn.__name__} failed (rc={rc}): {_lib.last_error()}")
+            col = 0
+            for buf, cout in self._emb_outs:
+                table[r0:r0 + n, col:col + cout].copy_(buf[:n])
+                col += cout
+        self.t_in.copy_(saved)
+        self._emb_table, self._emb_rows = table, rows
+        self.calls[self._emb_gather_idx] = (self.lib.seva_emb_gather, (table.data_ptr(), self._emb_cols, rows,
+                                                                       self.t_in.data_ptr(), self.N,
+                                                                       self._emb_desc.data_ptr(), len(self._emb_outs)))
+        self._graphs.clear()
+        self._eager_runs.clear()
 
     def _launch_all(self, skip, stream) -> None:
         for i, (fn, args) in enumerate(self.calls):
@@ -1043,10 +1105,12 @@ class Engine:
                 return self.run(timing)
         stream = torch.cuda.current_stream().cuda_stream
         timing = self.timing_sink if timing is None else timing
-        skip = self._invariant if self._skip_invariant else ()
+        skip = set(self._invariant) if self._skip_invariant else set()
+        if self._emb_gather_idx is not None:
+            skip |= self._emb_calls if self._use_emb_table else {self._emb_gather_idx}
         if timing is None:
             if self.use_graph:
-                variant = bool(self._skip_invariant)
+                variant = (bool(self._skip_invariant), self._use_emb_table)
                 g = self._graphs.get(variant)
                 if g is None and self._eager_runs.get(variant, 0) >= 1 and not torch.cuda.is_current_stream_capturing():
                     g = self._capture(skip)

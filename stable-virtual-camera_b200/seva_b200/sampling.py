@@ -167,7 +167,7 @@ class DiscreteDenoiser(object):
             blended = torch.empty((n, 4, h, w), device=input.device, dtype=torch.float32)
             ops.denoise_prepare(input.float().contiguous(), None if replace is None else replace.float().contiguous(),
                                 cond["concat"].float().contiguous(), c_in, eng.net_in, blended, n, n, h, w)
-            eng.bind(idx, cond["crossattn"], cond["dense_vector"], epoch=cond.get(COND_EPOCH))
+            eng.bind(idx, cond["crossattn"], cond["dense_vector"], epoch=cond.get(COND_EPOCH), t_range=self.sigmas.numel())
             eng.run()
             out = torch.empty_like(blended)
             ops.denoise_finish(eng.eps, blended, c_out, out, n, h, w)
@@ -184,10 +184,11 @@ class DiscreteDenoiser(object):
                             eng.net_in, blended, nl, nl, h, w)
         epoch = cond.get(COND_EPOCH)
         if eng.cond_current(epoch):
-            eng.bind(sh.local(idx, B), None, None, epoch=epoch)
+            eng.bind(sh.local(idx, B), None, None, epoch=epoch, t_range=self.sigmas.numel())
         else:
             ctx = cond["crossattn"].float()
-            eng.bind(sh.local(idx, B), sh.local(ctx, B), loc(cond["dense_vector"]), ctx0=ctx[::num_frames], epoch=epoch)
+            eng.bind(sh.local(idx, B), sh.local(ctx, B), loc(cond["dense_vector"]), ctx0=ctx[::num_frames], epoch=epoch,
+                     t_range=self.sigmas.numel())
         eng.run()
         out_l = torch.empty_like(blended)
         ops.denoise_finish(eng.eps, blended, loc(c_out), out_l, nl, h, w)

@@ -415,6 +415,30 @@ def test_cross_attention_with_several_context_tokens_vs_oracle(ntok):
     assert err < NET_TOL, err
 
 
+def test_timestep_table_is_bit_identical(monkeypatch):
+    """N2: `emb_layers(time_embed(timestep_embedding(t)))` served from the per-sigma-index table (one gather per step) vs
+    computed per step: the table rows come out of the same launches, so the sampled latents must be equal bit for bit."""
+    from seva_b200 import sampling as S
+    from seva_b200.model import SevaParams
+
+    T, h, w, steps = 3, 16, 16, 4
+    P = SevaParams(model_channels=64, num_frames=T)
+    inp = synth.make_inputs(T, 1, h, w, O.plucker, seed=8, num_steps=steps, ctx_dim=P.context_dim)
+    outs, launches = [], []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("SEVA_EMB_TABLE", flag)
+        model, _ = build_model(P, seed=21)
+        x, cap = _sample_ours(model, inp, T, steps, 2.0, S.MultiviewCFG(1.2))
+        eng = next(iter(model.module._engines.values()))
+        assert (eng._emb_table is not None) == (flag == "1")
+        outs.append((x.clone(), [c.clone() for c in cap]))
+        launches.append(eng.n_launch_step)
+    assert torch.equal(outs[0][0], outs[1][0])
+    for a, b in zip(outs[0][1], outs[1][1]):
+        assert torch.equal(a, b)
+    assert launches[0] == launches[1] - 3, launches  # t-emb + 2 GEMVs + grouped GEMV -> one gather
+
+
 def test_tiny_50_steps_final_latents_vs_oracle(tiny):
     """north_star: final latents within rel-L2 5e-2 of the fp32 reference after the full 50-step schedule (tiny network
     here; tools/parity_50step.py runs the same check at BASELINE configs[1] size against the oracle on the GPU)."""
