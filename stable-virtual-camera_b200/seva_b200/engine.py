@@ -13,6 +13,7 @@ loop of foreign calls with constant arguments (and is CUDA-graph capturable).
 from __future__ import annotations
 
 import ctypes as C
+import math
 import os
 
 import torch
@@ -38,14 +39,37 @@ def _pack_ff(ff, dev):
     return dict(w1=wp, b1=bp, bn1=bn, w2=pack.pack_linear(ff.net[2].weight), b2=_f32(ff.net[2].bias))
 
 
-def _pack_attn_self(at):
-    return dict(wqkv=pack.pack_linear(torch.cat([at.to_q.weight, at.to_k.weight, at.to_v.weight], 0)),
-                wo=pack.pack_linear(at.to_out[0].weight), bo=_f32(at.to_out[0].bias))
+def _no_launch(*_args) -> int:
+    """placeholder plan entry (the timestep-table gather before its table exists)"""
+    return 0
 
 
-def _pack_attn_cross(at):
-    return dict(wq=pack.pack_linear(at.to_q.weight), wk=pack.pack_linear(at.to_k.weight),
-                wv=pack.pack_linear(at.to_v.weight), wo=pack.pack_linear(at.to_out[0].weight),
+def _pad_head_rows(w, heads, dh):
+    """[heads * dh, K] -> [heads * 64, K]: every head's rows followed by 64 - dh zero rows (dh <= 64)."""
+    if dh == 64:
+        return w
+    out = w.new_zeros(heads, 64, w.shape[1])
+    out[:, :dh] = w.reshape(heads, dh, w.shape[1])
+    return out.reshape(heads * 64, w.shape[1])
+
+
+def _pad_head_cols(w, heads, dh):
+    """[N, heads * dh] -> [N, heads * 64] with zero columns at the padded head dimensions."""
+    return w if dh == 64 else _pad_head_rows(w.t(), heads, dh).t()
+
+
+def _pack_attn_self(at, heads=None, dh=64):
+    hp = lambda w: _pad_head_rows(w.detach(), heads, dh)
+    return dict(wqkv=pack.pack_linear(torch.cat([hp(at.to_q.weight), hp(at.to_k.weight), hp(at.to_v.weight)], 0)),
+                wo=pack.pack_linear(_pad_head_cols(at.to_out[0].weight.detach(), heads, dh)), bo=_f32(at.to_out[0].bias))
+
+
+def _pack_attn_cross(at, heads=None, dh=64):
+    hp = lambda w: pack.pack_linear(_pad_head_rows(w.detach(), heads, dh))
+    # wv1 / wo1: the unpadded pair of the single-context-token shortcut (to_out(to_v(ctx)), no head structure)
+    return dict(wq=hp(at.to_q.weight), wk=hp(at.to_k.weight), wv=hp(at.to_v.weight),
+                wo=pack.pack_linear(_pad_head_cols(at.to_out[0].weight.detach(), heads, dh)),
+                wv1=pack.pack_linear(at.to_v.weight), wo1=pack.pack_linear(at.to_out[0].weight),
                 bo=_f32(at.to_out[0].bias))
 
 
@@ -119,18 +143,19 @@ def pack_weights(model: Seva) -> dict:
                     d["bs"] = _f32(m.skip_connection.bias)
                 P[id(m)] = d
             elif isinstance(m, MultiviewTransformer):
-                fold = _can_fold(m.in_channels)
+                fold = _can_fold(m.in_channels) and m.d_head == 64
+                hd = dict(heads=m.n_heads, dh=m.d_head)
                 pairs = []
                 for tb, tm in zip(m.transformer_blocks, m.time_mix_blocks):   # transformer_depth pairs (transformer.py:234)
                     pairs.append(dict(
-                        s_attn1=_pack_attn_self_ln(tb.attn1, tb.norm1) if fold else _pack_attn_self(tb.attn1),
-                        s_attn2=_pack_attn_cross(tb.attn2),
+                        s_attn1=_pack_attn_self_ln(tb.attn1, tb.norm1) if fold else _pack_attn_self(tb.attn1, **hd),
+                        s_attn2=_pack_attn_cross(tb.attn2, **hd),
                         s_ff=_pack_ff_ln(tb.ff, tb.norm3) if fold else _pack_ff(tb.ff, dev),
                         s_n1=_pack_ln(tb.norm1), s_n2=_pack_ln(tb.norm2), s_n3=_pack_ln(tb.norm3),
                         t_nin=_pack_ln(tm.norm_in),
                         t_ffin=_pack_ff_ln(tm.ff_in, tm.norm_in) if fold else _pack_ff(tm.ff_in, dev),
-                        t_attn1=_pack_attn_self_ln(tm.attn1, tm.norm1) if fold else _pack_attn_self(tm.attn1),
-                        t_attn2=_pack_attn_cross(tm.attn2),
+                        t_attn1=_pack_attn_self_ln(tm.attn1, tm.norm1) if fold else _pack_attn_self(tm.attn1, **hd),
+                        t_attn2=_pack_attn_cross(tm.attn2, **hd),
                         t_ff=_pack_ff_ln(tm.ff, tm.norm3) if fold else _pack_ff(tm.ff, dev),
                         t_n1=_pack_ln(tm.norm1), t_n2=_pack_ln(tm.norm2), t_n3=_pack_ln(tm.norm3)))
                 P[id(m)] = dict(
@@ -660,7 +685,7 @@ class Engine:
             self._emb_desc = desc.to(self.dev)
             self._emb_cols = col
             self._emb_gather_idx = pos
-            self.calls.insert(pos, (None, ()))   # filled in when the table exists; skipped until then
+            self.calls.insert(pos, (_no_launch, ()))   # replaced when the table exists; a no-op until then
             self.meta.insert(pos, ("seva_emb_gather", "emb table", 0.0, 0.0))
             self._invariant = {i + 1 if i >= pos else i for i in self._invariant}
             self._emb_calls = {i + 1 if i >= pos else i for i in self._emb_calls}
@@ -816,8 +841,8 @@ class Engine:
         R = ctx_rows.shape[0]
         v = self.buf(f"xv_{tag}", R, C_, F32)
         o = self.buf(f"xo_{tag}", R, C_, F32)
-        self.gemv(ctx_rows, wa["wv"], None, v, group="cross_v")
-        self.gemv(v, wa["wo"], wa["bo"], o, group="cross_o")
+        self.gemv(ctx_rows, wa["wv1"], None, v, group="cross_v")
+        self.gemv(v, wa["wo1"], wa["bo"], o, group="cross_o")
         return o
 
     def _rows(self, l, C_):
@@ -844,6 +869,10 @@ class Engine:
     def _mvt(self, m: MultiviewTransformer, x, l, out):
         w = self.P[id(m)]
         C_, heads = m.in_channels, m.n_heads
+        # heads narrower than 64 run zero-padded to 64 (packed weights carry the padding; the padded score / output
+        # dimensions contribute exact zeros): Ci is the padded inner width, the softmax scale stays 1 / sqrt(d_head)
+        Ci, sc = heads * 64, 1.0 / math.sqrt(m.d_head)
+        self._attn_scale = sc
         H, Wd = self.HW[l]
         S = H * Wd
         rc = self.rows_c(l)
@@ -870,8 +899,8 @@ class Engine:
             if not fold:
                 self.ln(x0, pw["s_n1"], a)
             qkv_in = dict(A=x0, ln=dict(ln_in=rows, ln_eps=pw["s_attn1"]["eps"])) if fold else dict(A=a, ln={})
-            qkv = self.buf(f"tk_qkv_{l}", rc, 3 * C_)
-            o = self.buf(f"tk_o_{l}", rc, C_)
+            qkv = self.buf(f"tk_qkv_{l}", rc, 3 * Ci)
+            o = self.buf(f"tk_o_{l}", rc, Ci)
             bat, Lseq = (B, T * S) if is3d else (self.N, S)
             sh = self.shard
             if is3d and sh is not None:
@@ -882,27 +911,27 @@ class Engine:
                     box = {}
 
                     def after_kv(q_, kvl_):
-                        box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, C_, mode=ring)
+                        box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, Ci, mode=ring)
                         self.add(_RingStart(box["ring"]), tag="start")
 
-                    q, kvl, _ = self._split_qkv(qkv_in, pw["s_attn1"], l, C_, S, gather=False, after_kv=after_kv)
+                    q, kvl, _ = self._split_qkv(qkv_in, pw["s_attn1"], l, Ci, S, gather=False, after_kv=after_kv)
                     self.add(box["ring"],
-                             flops=4.0 * bat * heads * Lseq * Lk * 64, nbytes=2.0 * bat * Lk * 2 * C_,
+                             flops=4.0 * bat * heads * Lseq * Lk * 64, nbytes=2.0 * bat * Lk * 2 * Ci,
                              tag=f"attn3d+exchange B{bat} H{heads} Lq{Lseq} Lk{Lk} {ring}")
                     self._touch_forward(q, o)
                 else:
-                    q, kvl, kvf = self._split_qkv(qkv_in, pw["s_attn1"], l, C_, S)
-                    self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_, o.data_ptr(), bat,
-                             heads, Lseq, Lk, C_, 2 * C_, 2 * C_, o.stride(0), Lseq * C_, Lk * 2 * C_, Lk * 2 * C_,
-                             Lseq * o.stride(0), 0.125, flops=4.0 * bat * heads * Lseq * Lk * 64,
+                    q, kvl, kvf = self._split_qkv(qkv_in, pw["s_attn1"], l, Ci, S)
+                    self.add(self.lib.seva_attn_fwd, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * Ci, o.data_ptr(), bat,
+                             heads, Lseq, Lk, Ci, 2 * Ci, 2 * Ci, o.stride(0), Lseq * Ci, Lk * 2 * Ci, Lk * 2 * Ci,
+                             Lseq * o.stride(0), sc, flops=4.0 * bat * heads * Lseq * Lk * 64,
                              tag=f"attn3d B{bat} H{heads} Lq{Lseq} Lk{Lk}")
                     self._touch_forward(q, kvf, o)
             else:
                 self._qkv(qkv_in, pw["s_attn1"], slice(None), qkv)
                 ld = qkv.stride(0)
                 base = qkv.data_ptr()
-                self.add(self.lib.seva_attn_fwd, base, base + 2 * C_, base + 4 * C_, o.data_ptr(), bat, heads, Lseq, Lseq,
-                         ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), 0.125,
+                self.add(self.lib.seva_attn_fwd, base, base + 2 * Ci, base + 4 * Ci, o.data_ptr(), bat, heads, Lseq, Lseq,
+                         ld, ld, ld, o.stride(0), Lseq * ld, Lseq * ld, Lseq * ld, Lseq * o.stride(0), sc,
                          flops=4.0 * bat * heads * Lseq * Lseq * 64,
                          tag=("attn3d" if is3d else "attn2d") + f" B{bat} H{heads} L{Lseq}")
                 self._touch_forward(qkv, o)
@@ -914,7 +943,7 @@ class Engine:
             else:
                 x1a = self.buf(f"tk_x1a_{l}", rc, C_)
                 self.gemm(o, pw["s_attn1"]["wo"], x1a, bias=pw["s_attn1"]["bo"], residual=x0)
-                self._cross_general(pw["s_attn2"], pw["s_n2"], x1a, x1, l, C_, heads, bat, Lseq,
+                self._cross_general(pw["s_attn2"], pw["s_n2"], x1a, x1, l, Ci, heads, bat, Lseq,
                                     self.ctx0_in if is3d else self.ctx_in, out_rows=rows)
             x2 = self.buf(f"tk_x2_{l}", rc, C_)
             self._ff(x1, pw["s_n3"], pw["s_ff"], x1, x2, l, C_, "s", x_rows=rows, out_rows=rows)
@@ -929,27 +958,27 @@ class Engine:
                 sa, sb = sh.space_parts(S)[sh.rank]
                 S_me = sb - sa
                 self._qkv(qkv_in, pw["t_attn1"], slice(None), qkv)
-                qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * C_)
-                o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, C_)
+                qkv_sp = self.buf(f"tk_qkv_sp_{l}", B * self.Tk * S_me, 3 * Ci)
+                o_sp = self.buf(f"tk_o_sp_{l}", B * self.Tk * S_me, Ci)
                 self.add(_SpaceExchange(sh, True, qkv, qkv_sp, B, S), nbytes=2.0 * (qkv.numel() + qkv_sp.numel()),
                          tag=f"to_space rows{rc} C{3 * C_}")
                 self.add(self.lib.seva_timemix_attn, qkv_sp.data_ptr(), o_sp.data_ptr(), B, self.Tk, S_me, heads,
-                         qkv_sp.stride(0), o_sp.stride(0), 0.125, flops=4.0 * B * S_me * heads * self.Tk * self.Tk * 64,
+                         qkv_sp.stride(0), o_sp.stride(0), sc, flops=4.0 * B * S_me * heads * self.Tk * self.Tk * 64,
                          nbytes=2.0 * 4 * qkv_sp.shape[0] * C_, tag=f"timemix BS{B * S_me} H{heads} T{self.Tk}")
                 self.add(_SpaceExchange(sh, False, o_sp, o, B, S), nbytes=2.0 * (o_sp.numel() + o.numel()),
                          tag=f"to_frames rows{rc} C{C_}")
                 self._touch_forward(qkv, o)
             elif sh is not None:
-                q, kvl, kvf = self._split_qkv(qkv_in, pw["t_attn1"], l, C_, S)
-                self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * C_,
-                         o.data_ptr(), B, T, self.Tk, S, heads, C_, 2 * C_, o.stride(0), 0.125,
+                q, kvl, kvf = self._split_qkv(qkv_in, pw["t_attn1"], l, Ci, S)
+                self.add(self.lib.seva_timemix_attn_kv, q.data_ptr(), kvf.data_ptr(), kvf.data_ptr() + 2 * Ci,
+                         o.data_ptr(), B, T, self.Tk, S, heads, Ci, 2 * Ci, o.stride(0), sc,
                          flops=4.0 * B * S * heads * T * self.Tk * 64, nbytes=2.0 * (2 * rc + 2 * B * self.Tk * S) * C_,
                          tag=f"timemix BS{B * S} H{heads} Tq{T} Tk{self.Tk}")
                 self._touch_forward(q, kvf, o)
             else:
                 self._qkv(qkv_in, pw["t_attn1"], slice(None), qkv)
                 self.add(self.lib.seva_timemix_attn, qkv.data_ptr(), o.data_ptr(), B, T, S, heads, qkv.stride(0),
-                         o.stride(0), 0.125, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
+                         o.stride(0), sc, flops=4.0 * B * S * heads * T * T * 64, nbytes=2.0 * 4 * rc * C_,
                          tag=f"timemix BS{B * S} H{heads}")
                 self._touch_forward(qkv, o)
             y2 = self.buf(f"tk_y2_{l}", rc, C_)
@@ -963,7 +992,7 @@ class Engine:
                 # token order needs no transpose: batch = B, T * S queries each
                 y2a = self.buf(f"tk_x1a_{l}", rc, C_)
                 self.gemm(o, pw["t_attn1"]["wo"], y2a, bias=pw["t_attn1"]["bo"], residual=y1)
-                self._cross_general(pw["t_attn2"], pw["t_n2"], y2a, y2, l, C_, heads, B, T * S, self.ctx0_in, out_rows=rows)
+                self._cross_general(pw["t_attn2"], pw["t_n2"], y2a, y2, l, Ci, heads, B, T * S, self.ctx0_in, out_rows=rows)
             x3 = self.buf(f"tk_x3_{l}", rc, C_)
             # x = x_spatial + ff(norm3(y2)): SkipConnect (transformer.py:158-165) folded into the residual
             self._ff(y2, pw["t_n3"], pw["t_ff"], x2, x3, l, C_, "t", x_rows=rows, out_rows=rows if more else None)
@@ -1001,7 +1030,8 @@ class Engine:
     def _cross_general(self, wa, nrm, xin, xout, l, C_, heads, bat, Lseq, ctx, out_rows=None):
         """attn2 with Lk > 1 context tokens: LN -> q, k/v from context -> flash attention -> to_out + residual."""
         rc = xin.shape[0]
-        a = self.buf(f"tk_ln_{l}", rc, C_)
+        sc = self._attn_scale
+        a = self.buf(f"tk_ln_{l}", rc, xin.shape[1])
         self.ln(xin, nrm, a)
         q = self.buf(f"tk_q_{l}", rc, C_)
         self.gemm(a, wa["wq"], q)
@@ -1015,7 +1045,7 @@ class Engine:
         o = self.buf(f"tk_o2_{l}", rc, C_)
         assert R == bat
         self.add(self.lib.seva_attn_fwd, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), bat, heads, Lseq,
-                 self.L, C_, C_, C_, C_, Lseq * C_, self.L * C_, self.L * C_, Lseq * C_, 0.125,
+                 self.L, C_, C_, C_, C_, Lseq * C_, self.L * C_, self.L * C_, Lseq * C_, sc,
                  flops=4.0 * bat * heads * Lseq * self.L * 64, tag="attn_cross")
         self._touch_forward(q, o)
         self.gemm(o, wa["wo"], xout, bias=wa["bo"], residual=xin, ln_rows=out_rows)

@@ -153,9 +153,11 @@ class Seva(nn.Module):
     def __init__(self, params: SevaParams) -> None:
         super().__init__()
         p = params
-        if p.num_head_channels != 64:  # the tcgen05 attention and time-mix kernels are built for 64-wide heads
-            raise SevaB200Error(f"num_head_channels={p.num_head_channels}: seva_b200 supports head width 64 only "
-                                "(the released Seva configuration); there is no generic fallback")
+        if not (8 <= p.num_head_channels <= 64 and p.num_head_channels % 8 == 0):
+            # the tcgen05 attention and time-mix kernels are built for 64-wide heads; narrower heads run zero-padded to 64
+            # (engine._pad_head_rows), wider ones have no kernel
+            raise SevaB200Error(f"num_head_channels={p.num_head_channels}: seva_b200 supports head widths 8, 16, ..., 64 "
+                                "(64 is the released Seva configuration); there is no generic fallback")
         if p.model_channels % 64 != 0:
             raise SevaB200Error(f"model_channels={p.model_channels} must be a multiple of 64 (head width / GEMM K tiles)")
         self.params = p

@@ -415,6 +415,44 @@ def test_cross_attention_with_several_context_tokens_vs_oracle(ntok):
     assert err < NET_TOL, err
 
 
+@pytest.mark.parametrize("dh", [32, 16])
+def test_narrow_heads_run_zero_padded(dh):
+    """num_head_channels < 64 (seva/model.py:156-160; the released model uses 64): every head runs zero-padded to the
+    kernels' width 64 with the softmax scale of its true width -- spatial 2D / 3D, time-mix and cross attention."""
+    from seva_b200 import sampling as S
+    from seva_b200.model import SevaParams
+
+    T, h, w = 3, 16, 16
+    P = SevaParams(model_channels=64, num_frames=T, num_head_channels=dh)
+    model, sd = build_model(P, seed=13)
+    inp = synth.make_inputs(T, 1, h, w, O.plucker, seed=5, num_steps=1, ctx_dim=P.context_dim)
+    x, cap = _sample_ours(model, inp, T, 1, 2.0, S.MultiviewCFG(1.2))
+    table = O.denoiser_table()
+    fs = O.multiview_scale(2.0, 1.2, inp["c2w"], inp["K"], inp["mask"])
+    net = lambda xx, idx, c: O.sgm_forward(sd, P, xx, idx, c, num_frames=T)
+    with torch.inference_mode():
+        sig = torch.cat([O.ddpm_sigmas(1), torch.zeros(1)])
+        x0 = inp["x0"] * torch.sqrt(1.0 + sig[0] ** 2.0)
+        ones = torch.ones(T)
+        _, den0 = O.sampler_step(net, table, x0, ones * sig[0], ones * sig[1], fs, inp["c"], inp["uc"], inp["eps"][0])
+    u, c = cap[0].float().cpu().chunk(2)
+    den_ours = u + fs.view(-1, 1, 1, 1) * (c - u)
+    err = rel_l2(den_ours, den0)
+    print(f"head width {dh}: denoiser rel-L2 {err:.3e}")
+    assert err < NET_TOL, err
+    # several context tokens through the general cross-attention path with padded heads
+    cc = {k: torch.cat((inp["uc"][k], inp["c"][k]), 0) for k in ("crossattn", "concat", "dense_vector")}
+    g = torch.Generator().manual_seed(9)
+    cc["crossattn"] = torch.randn(2 * T, 3, P.context_dim, generator=g)
+    xx = torch.randn(2 * T, 4, h, w, generator=g)
+    tt = torch.full((2 * T,), 500, dtype=torch.int64)
+    with torch.inference_mode(), torch.autocast("cuda"):
+        got = model(xx.cuda(), tt.cuda(), {k: v.cuda() for k, v in cc.items()}, num_frames=T)
+    with torch.inference_mode():
+        ref = O.sgm_forward(sd, P, xx, tt, cc, num_frames=T)
+    assert rel_l2(got.float().cpu(), ref) < NET_TOL
+
+
 def test_timestep_table_is_bit_identical(monkeypatch):
     """N2: `emb_layers(time_embed(timestep_embedding(t)))` served from the per-sigma-index table (one gather per step) vs
     computed per step: the table rows come out of the same launches, so the sampled latents must be equal bit for bit."""

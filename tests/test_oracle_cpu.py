@@ -172,7 +172,7 @@ def test_no_cpu_fallback():
         m(torch.zeros(6, 11, 16, 16), torch.zeros(6, dtype=torch.long), torch.zeros(6, 1, 1024),
           torch.zeros(6, 6, 16, 16), num_frames=3)
     from seva_b200.model import SevaParams
-    for bad in (dict(num_head_channels=32), dict(model_channels=96)):  # unsupported configurations fail at construction
+    for bad in (dict(num_head_channels=128), dict(num_head_channels=20), dict(model_channels=96)):  # unsupported configurations fail at construction
         with pytest.raises(_lib.SevaB200Error):
             Seva(SevaParams(**bad))
     if not torch.cuda.is_available():
