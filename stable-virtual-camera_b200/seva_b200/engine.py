@@ -270,10 +270,10 @@ class _RingAttention:
     """
     __name__ = "ring_attn3d"
 
-    def __init__(self, lib, shard: FrameShard, q, kvl, o, B, heads, S, C_, mode="ring"):
+    def __init__(self, lib, shard: FrameShard, q, kvl, o, B, heads, S, C_, mode="ring", scale=0.125):
         self.lib, self.shard, self.q, self.kvl, self.o = lib, shard, q, kvl, o
         self.B, self.heads, self.S, self.C = B, heads, S, C_
-        self.mode = mode
+        self.mode, self.scale = mode, float(scale)   # scale: 1 / sqrt(true head width), narrow heads run zero-padded
         dev, P = q.device, shard.size
         self.Lq = shard.T_local * S
         self.parts = torch.empty(P, B, self.Lq, C_, device=dev, dtype=F32)
@@ -337,7 +337,7 @@ class _RingAttention:
             kv, Lk, bs = self.block(r)
             rc = self.lib.seva_attn_partial(self.q.data_ptr(), kv.data_ptr(), kv.data_ptr() + 2 * self.C,
                                             self.parts[r].data_ptr(), self.lse[r].data_ptr(), self.B, self.heads, self.Lq,
-                                            Lk, self.C, 2 * self.C, 2 * self.C, self.Lq * self.C, bs, bs, 0.125, stream)
+                                            Lk, self.C, 2 * self.C, 2 * self.C, self.Lq * self.C, bs, bs, self.scale, stream)
             if rc:
                 return rc
         return self.lib.seva_attn_merge(self.parts.data_ptr(), self.lse.data_ptr(), self.o.data_ptr(), P, self.B, self.heads,
@@ -481,9 +481,11 @@ class Engine:
         # The plan is static (constant pointers and sizes), so after one eager run per variant (all launches / the
         # conditioning-only launches skipped) it is captured into a CUDA graph and replayed: one driver call per forward
         # instead of ~600 ctypes calls, each with its cuTensorMapEncodeTiled (the descriptors are baked into the
-        # captured kernel parameters).  Not used with a frame shard (its collectives go through torch.distributed) or
-        # while per-launch timing is on.  SEVA_CUDA_GRAPH=0 turns it off.
-        self.use_graph = os.environ.get("SEVA_CUDA_GRAPH", "1") != "0" and shard is None
+        # captured kernel parameters).  Not used while per-launch timing is on; SEVA_CUDA_GRAPH=0 turns it off.  With a
+        # frame shard the plan holds torch.distributed collectives: capturing those is opt-in (SEVA_SHARD_GRAPH=1, every
+        # rank alike).
+        self.use_graph = os.environ.get("SEVA_CUDA_GRAPH", "1") != "0" and (
+            shard is None or os.environ.get("SEVA_SHARD_GRAPH", "0") == "1")
         self._graphs: dict = {}
         self._eager_runs: dict = {}
 
@@ -911,7 +913,7 @@ class Engine:
                     box = {}
 
                     def after_kv(q_, kvl_):
-                        box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, Ci, mode=ring)
+                        box["ring"] = _RingAttention(self.lib, sh, q_, kvl_, o, bat, heads, S, Ci, mode=ring, scale=sc)
                         self.add(_RingStart(box["ring"]), tag="start")
 
                     q, kvl, _ = self._split_qkv(qkv_in, pw["s_attn1"], l, Ci, S, gather=False, after_kv=after_kv)
@@ -1123,7 +1125,8 @@ class Engine:
         """Record the plan (minus ``skip``) into a CUDA graph.  Nothing is allocated while capturing (every workspace
         exists already) and the launches only enqueue kernels, so the capture itself does no work: the caller replays."""
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # thread_local: NCCL's watchdog thread may call the runtime while a sharded plan is being captured
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
             self._launch_all(skip, torch.cuda.current_stream().cuda_stream)
         return g
 
