@@ -137,6 +137,22 @@ int seva_timemix_attn_kv(const void* q, const void* k, const void* v, void* out,
 int64_t seva_groupnorm_stats_floats(int32_t Nimg, int32_t rpi, int32_t C);
 int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
                          float* sums, int32_t reverse, void* stream);
+/* seva_groupnorm_stats for callers that cannot allocate a workspace (code under CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernel, same launch shape and therefore the same bits as seva_groupnorm_stats, but the per-block partials and
+ * the tickets live in a device array inside the library (SEVA_GN_STATS_STATIC_MAX_FLOATS floats of partials +
+ * SEVA_GN_STATS_STATIC_MAX_IMAGES tickets = 16 MiB + 4 KiB, held by every GPU that loads the library until exit), so
+ * the caller passes only x and `totals`: fp32 [Nimg, C, 2] (sum, sum of squares), 16-byte aligned, what
+ * seva_groupnorm_apply reads as `sums`.  The call allocates nothing (no cudaMalloc / cudaFree).  A problem that needs
+ * more scratch (Nimg > SEVA_GN_STATS_STATIC_MAX_IMAGES, or Nimg * blocks-per-image * C * 2 floats of partials beyond
+ * the maximum -- every GroupNorm of the T=21 Seva step fits: 42 images of up to 2560 channels need 3.0 M floats) is
+ * rejected with return code 1 and a message naming the limit.  All calls share the one array, which keeps the last
+ * call's contents (the entry point clears the tickets itself): calls that OVERLAP on the GPU (different streams with
+ * no ordering between them, or two host threads) race; serialise them on one stream or with events. */
+#define SEVA_GN_STATS_STATIC_MAX_FLOATS (1 << 22)
+#define SEVA_GN_STATS_STATIC_MAX_IMAGES 1024
+int seva_groupnorm_stats_static(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
+                                float* totals, int32_t reverse, void* stream);
 typedef struct SevaGNApply {
   const void* x; int64_t ldx;     /* bf16 input, zero-bordered flat (in_padded=1) or compact rows        */
   void* y; int64_t ldy;           /* bf16 output                                                          */

@@ -953,6 +953,70 @@ extern "C" int seva_groupnorm_stats(const void* x, int64_t ldx, int32_t Nimg, in
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// seva_groupnorm_stats_static: the statistics kernel for callers that cannot allocate (no counterpart in the reference).
+// The per-block partials and the per-image tickets live in a file-scope
+// device array instead of a caller's workspace; the caller passes only the input and the [Nimg, C, 2] totals.
+// Every GPU that loads the library holds the array (16 MiB + 4 KiB) until exit.  All calls share it: two calls that
+// overlap on the GPU (different streams, no ordering between them) race on the partials and tickets.
+// ------------------------------------------------------------------------------------------------
+constexpr long long kStaticStatsFloats = SEVA_GN_STATS_STATIC_MAX_FLOATS;    // per-block partials
+constexpr int kStaticStatsTickets = SEVA_GN_STATS_STATIC_MAX_IMAGES;         // one ticket per image
+static __device__ __align__(256) float g_gn_stats_scratch[kStaticStatsFloats + kStaticStatsTickets];
+
+// Device address of g_gn_stats_scratch on the current device.  In host code the symbol's name is a host-side stand-in, not a
+// device address, so it is looked up once per device (with that device current) and cached; thread-safe.
+static int gn_static_scratch(float** out) {
+  static std::mutex mu;
+  static float* cache[64];
+  int dev = -1;
+  SEVA_CUDA(cudaGetDevice(&dev));
+  SEVA_CHECK(dev >= 0 && dev < 64, "seva_groupnorm_stats_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache[dev] == nullptr) {
+    float* p = nullptr;
+    SEVA_CUDA(cudaGetSymbolAddress((void**)&p, g_gn_stats_scratch));
+    SEVA_CHECK(p != nullptr, "seva_groupnorm_stats_static: cudaGetSymbolAddress returned a null address");
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return 0;
+}
+
+extern "C" int seva_groupnorm_stats_static(const void* x, int64_t ldx, int32_t Nimg, int32_t rpi, int32_t C,
+                                           float* totals, int32_t reverse, void* stream_v) {
+  using namespace seva;
+  if (check_device()) return 3;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_v);
+  SEVA_CHECK(x && totals, "seva_groupnorm_stats_static: null pointer");
+  SEVA_CHECK(Nimg > 0 && rpi > 0 && C > 0 && (C % 8) == 0 && (ldx % 8) == 0,
+             "seva_groupnorm_stats_static: need C %% 8 == 0 and ldx %% 8 == 0 (C=%d ldx=%lld)", C, (long long)ldx);
+  SEVA_CHECK(C / 8 <= 512, "seva_groupnorm_stats_static: C too large (%d)", C);
+  SEVA_CHECK(((uintptr_t)x & 15) == 0 && ((uintptr_t)totals & 15) == 0,
+             "seva_groupnorm_stats_static: x and totals must be 16-byte aligned");
+  int rpb, rows, nblk;
+  gn_stats_shape(Nimg, rpi, C, &rpb, &rows, &nblk);
+  const long long need = (long long)Nimg * nblk * C * 2;
+  SEVA_CHECK(Nimg <= kStaticStatsTickets,
+             "seva_groupnorm_stats_static: %d images exceed the static scratch (max %d images); use seva_groupnorm_stats "
+             "with a caller-owned workspace", Nimg, kStaticStatsTickets);
+  SEVA_CHECK(need <= kStaticStatsFloats,
+             "seva_groupnorm_stats_static: Nimg=%d rpi=%d C=%d needs %lld floats of per-block partials, the static scratch "
+             "holds %lld; use seva_groupnorm_stats with a caller-owned workspace", Nimg, rpi, C, need, kStaticStatsFloats);
+  float* scratch = nullptr;
+  if (int rc = gn_static_scratch(&scratch)) return rc;
+  int* tickets = reinterpret_cast<int*>(scratch + kStaticStatsFloats);
+  // the array keeps the last call's contents: the partials are fully overwritten before they are read, the tickets must
+  // start at zero (the kernel resets them, but a launch that was aborted would not have)
+  SEVA_CUDA(cudaMemsetAsync(tickets, 0, sizeof(int) * (size_t)Nimg, stream));
+  const int threads = (C / 8) * rpb;
+  dim3 grid(nblk, Nimg);
+  gn_stats_kernel<<<grid, threads, threads * 16 * sizeof(float), stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rpi, C, totals, scratch, tickets, rows, reverse != 0);
+  SEVA_CUDA(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int seva_groupnorm_partial_floats(int32_t Nimg, int32_t rpi, int32_t C) {
   if (Nimg <= 0 || rpi <= 0 || C <= 0) return -1;
   const long long n = (long long)Nimg * ((rpi + 31) / 32 + 1) * C * 2;

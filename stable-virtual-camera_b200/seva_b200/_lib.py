@@ -61,6 +61,7 @@ _PROTOS = {
     "seva_timemix_attn_kv": [c_void_p] * 4 + [c_int] * 5 + [c_i64] * 3 + [c_float, c_void_p],
     "seva_groupnorm_stats_floats": [c_int, c_int, c_int],
     "seva_groupnorm_stats": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_int, c_void_p],
+    "seva_groupnorm_stats_static": [c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_int, c_void_p],
     "seva_groupnorm_apply": [C.POINTER(SevaGNApply), c_void_p],
     "seva_groupnorm_partial_floats": [c_int, c_int, c_int],
     "seva_groupnorm_finalize": [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p,
