@@ -14,7 +14,9 @@ published algorithms:
     bias) -> [class_embedding; patches] + positional_embedding -> ln_pre -> `layers` ResidualAttentionBlocks
     (x += attn(ln_1 x); x += c_proj(gelu(c_fc(ln_2 x))), nn.MultiheadAttention with in_proj / out_proj, exact erf GELU)
     -> ln_post -> class token -> @ proj.
-The torch pieces the restatement leans on (F.interpolate, F.layer_norm, F.gelu, softmax) are the library calls the real
+`vit_forward` is checked against an independent implementation of the same architecture, Hugging Face transformers'
+CLIPVisionModelWithProjection with the weights converted key by key (tests/test_clip_hf_cpu.py, rel-L2 < 2e-5); the
+resize stays a restatement.  The torch pieces the restatement leans on (F.interpolate, F.layer_norm, F.gelu, softmax) are the library calls the real
 packages make themselves.
 """
 from __future__ import annotations
