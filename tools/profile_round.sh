@@ -7,7 +7,7 @@ MODE=${2:-all}   # all | list (launch list only)
 OUT=gpurun_out/prof_$TAG
 mkdir -p $OUT
 # warm-up 1: the ncu pass replays every launch of every bench pass (r1g: 22 k metric rows, 580 s of box time at --warmup 3)
-BENCH="python bench.py --steps 1 --warmup ${PROFILE_WARMUP:-1} --no-cpu"
+BENCH="python bench.py --steps 1 --warmup ${PROFILE_WARMUP:-1} --no-cpu ${PROFILE_BENCH_FLAGS:-}"
 # (1) launch list of one bench command: device time + DRAM bytes of every launch
 $BENCH > $OUT/plain_bench.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv \
