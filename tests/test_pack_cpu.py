@@ -120,3 +120,62 @@ def test_linear_and_1x1_weights_are_k_major_bf16():
     assert torch.equal(pack.pack_linear(w), w.bfloat16()) and pack.pack_linear(w).is_contiguous()
     w4 = torch.randn(12, 20, 1, 1)
     assert torch.equal(pack.pack_conv1x1(w4), w4.reshape(12, 20).bfloat16())
+
+
+# ---- engine-side packing: zero-padded narrow heads and the LayerNorm fold (host logic of engine.pack_weights) ----------
+class _Attn(torch.nn.Module):
+    def __init__(self, dim, inner):
+        super().__init__()
+        self.to_q, self.to_k, self.to_v = (torch.nn.Linear(dim, inner, bias=False) for _ in range(3))
+        self.to_out = torch.nn.ModuleList([torch.nn.Linear(inner, dim)])
+
+
+def test_narrow_heads_zero_padded_to_the_kernel_width():
+    """num_head_channels < 64: q / k / v rows and to_out columns are padded per head to 64; with the softmax scale of the
+    TRUE width the padded attention is the original one (the zero dimensions add nothing to q.k and produce zero outputs
+    that meet zero columns of to_out)."""
+    from seva_b200.engine import _pack_attn_self, _pad_head_cols, _pad_head_rows
+
+    torch.manual_seed(3)
+    for heads, dh in ((3, 16), (2, 32), (5, 8), (2, 64)):
+        dim, L = 40, 11
+        at = _Attn(dim, heads * dh)
+        p = _pack_attn_self(at, heads, dh)
+        assert p["wqkv"].shape == (3 * heads * 64, dim) and p["wo"].shape == (dim, heads * 64)
+        x = torch.randn(L, dim)
+        q, k, v = (x @ p["wqkv"].float().t()).view(L, 3, heads, 64).permute(1, 2, 0, 3)     # [heads, L, 64] each
+        o = torch.softmax(q @ k.transpose(-1, -2) / dh ** 0.5, -1) @ v
+        got = o.permute(1, 0, 2).reshape(L, heads * 64) @ p["wo"].float().t() + p["bo"]
+        r = lambda w: w.detach().bfloat16().float()
+        q0, k0, v0 = ((x @ r(m.weight).t()).view(L, heads, dh).transpose(0, 1) for m in (at.to_q, at.to_k, at.to_v))
+        o0 = F.scaled_dot_product_attention(q0[None], k0[None], v0[None])[0]
+        ref = o0.transpose(0, 1).reshape(L, heads * dh) @ r(at.to_out[0].weight).t() + at.to_out[0].bias
+        assert _rel(got, ref) < 1e-6
+        w = torch.randn(heads * dh, 7)
+        back = _pad_head_rows(w, heads, dh).view(heads, 64, 7)
+        assert torch.equal(back[:, :dh].reshape(heads * dh, 7), w) and not back[:, dh:].any()
+        assert torch.equal(_pad_head_cols(w.t(), heads, dh), _pad_head_rows(w, heads, dh).t())
+
+
+def test_layernorm_fold_identity():
+    """Linear(LayerNorm(x)) = rstd * (x W'^T - mean * colsum) + bias' with W' = W * gamma (bf16), colsum = sum_k W'[n, k],
+    bias' = W beta + b -- the form the GEMM epilogue applies (SevaGemm.ln_in_stats / ln_colsum)."""
+    from seva_b200.engine import _fold_ln_linear
+
+    torch.manual_seed(4)
+    C, N, M = 48, 20, 9
+    ln = torch.nn.LayerNorm(C)
+    with torch.no_grad():
+        ln.weight.copy_(1 + 0.2 * torch.randn(C))
+        ln.bias.copy_(0.1 * torch.randn(C))
+    w, b, x = torch.randn(N, C) / C ** 0.5, torch.randn(N) * 0.1, torch.randn(M, C) * 2 + 0.5
+    wg, colsum, bias2 = _fold_ln_linear(ln, w, b)
+    assert wg.dtype == torch.bfloat16
+    mean, var = x.mean(1, keepdim=True), x.var(1, unbiased=False, keepdim=True)
+    rstd = torch.rsqrt(var + ln.eps)
+    got = rstd * (x @ wg.float().t() - mean * colsum[None]) + bias2
+    gamma_w = wg.float() / ln.weight.detach()[None]          # the weight the fold effectively applies after rounding
+    ref = F.linear(F.layer_norm(x, (C,), ln.weight, ln.bias, ln.eps), gamma_w, b) - F.linear(ln.bias.detach()[None], gamma_w) \
+        + F.linear(ln.bias.detach()[None], w)
+    assert _rel(got, ref) < 1e-5
+    assert _rel(got, F.linear(F.layer_norm(x, (C,), ln.weight, ln.bias, ln.eps), w, b)) < 5e-3   # bf16 rounding of W * gamma
