@@ -173,7 +173,7 @@ def two_ranks():
         for p in procs:
             p.start()
         for p in procs:
-            p.join(120)
+            p.join(600)   # a cold `import torch` in a spawned worker alone can take a minute on a busy box
             assert p.exitcode == 0, f"worker exit code {p.exitcode}"
         yield {r: dict(ret[r]) for r in range(2)}
 

@@ -147,7 +147,7 @@ def test_run_scene_two_ranks_equals_one_rank(world):
         for p in procs:
             p.start()
         for p in procs:
-            p.join(240)
+            p.join(600)
             assert p.exitcode == 0, f"worker exit code {p.exitcode}"
         for r in range(world):
             assert torch.equal(ret[r]["two_pass"], want2), f"rank {r}: chunk-parallel second pass differs"
